@@ -1,0 +1,215 @@
+/* psvwave_b200 -- C ABI of the B200-native P-SV velocity-stress solver.
+ *
+ * This is the drop-in boundary for psvWave's solver core: every entry point below replaces
+ * one public member of the reference's C++ class `fdModel` (src/fdModel.h:35-318 of
+ * larsgeb/psvWave) or one accessor of its pybind11 wrapper (src/psvWave.cpp:85-458).  The
+ * reference-side binding a maintainer would add is shown in INTEGRATION.md; the pybind11
+ * module shipped here (psvwave_b200/csrc/pybind_module.cpp) is that binding.
+ *
+ * Conventions
+ *  - one opaque handle per fdModel object; a handle lives on ONE CUDA device (the device
+ *    that is current, or set with psv_set_default_device, when it is created);
+ *  - every call returns a status (0 = ok); the message of the last failure on the calling
+ *    thread is returned by psv_last_error();
+ *  - all pointers are HOST pointers owned by the caller unless the name says `device`;
+ *    getters copy out, setters copy in (the reference's getters return copies too,
+ *    src/psvWave.cpp:248-322);
+ *  - calls are synchronous from the caller's point of view;
+ *  - arrays are C-contiguous float64 with the reference's shapes: grid (nx, nz) with iz
+ *    fastest (src/contiguous_arrays.cpp:14-21), seismograms (n_shots, nr, nt), snapshots
+ *    (n_shots, snapshots, nx, nz);
+ *  - there is no CPU fallback: without a usable CUDA device creation fails with
+ *    PSV_ERR_CUDA.
+ */
+#ifndef PSVWAVE_B200_H
+#define PSVWAVE_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct psv_model *psv_handle;
+
+/* ---- status codes (mapped back to the reference's exception types by the binding) ---- */
+#define PSV_OK 0
+#define PSV_ERR_INVALID_ARGUMENT 1 /* std::invalid_argument  -> Python ValueError */
+#define PSV_ERR_LENGTH 2           /* std::length_error      -> Python ValueError */
+#define PSV_ERR_CUDA 3             /* CUDA runtime failure   -> Python RuntimeError */
+#define PSV_ERR_STATE 4            /* call order violated (e.g. adjoint without stored forward) */
+#define PSV_ERR_IO 5               /* file could not be written */
+
+const char *psv_last_error(void);
+const char *psv_version(void);
+
+/* ---- construction ------------------------------------------------------------------------
+ * psv_config mirrors the reference's explicit 30-argument constructor
+ * (src/fdModel.h:50-64; fdModel.cpp:29-62).  which_source_to_fire_in_which_shot is passed in
+ * CSR form: sources of shot s are shot_sources[shot_offsets[s] .. shot_offsets[s+1]).
+ * Source/receiver indices are relative to the physical domain (np_boundary is added by the
+ * library, src/fdModel.cpp:197-212). */
+typedef struct psv_config {
+  int nt, nx_inner, nz_inner, nx_inner_boundary, nz_inner_boundary;
+  double dx, dz, dt;
+  int np_boundary;
+  double np_factor;
+  double scalar_rho, scalar_vp, scalar_vs;
+  int npx, npz;
+  double peak_frequency, source_timeshift, delay_cycles_per_shot;
+  int n_sources, n_shots;
+  const int *ix_sources, *iz_sources;  /* [n_sources] */
+  const double *moment_angles;         /* [n_sources], degrees */
+  const int *shot_offsets;             /* [n_shots + 1] */
+  const int *shot_sources;             /* [shot_offsets[n_shots]] */
+  int nr;
+  const int *ix_receivers, *iz_receivers; /* [nr] */
+  int snapshot_interval;
+  const char *observed_data_folder, *stf_folder;
+} psv_config;
+
+/* fdModel::fdModel(const char*)  src/fdModel.cpp:16-27, .ini keys src/fdModel.cpp:470-523 */
+int psv_create_from_ini(const char *ini_path, psv_handle *out);
+/* fdModel::fdModel(30 args)      src/fdModel.cpp:29-62 */
+int psv_create(const psv_config *config, psv_handle *out);
+/* fdModel::fdModel(const fdModel&) src/fdModel.cpp:64-97,301-388 (deep copy incl. snapshots) */
+int psv_clone(psv_handle src, psv_handle *out);
+/* fdModel::~fdModel              src/fdModel.cpp:99-137 */
+int psv_destroy(psv_handle h);
+
+/* Host-only dry run of psv_create_from_ini: read + validate the .ini exactly as construction
+ * would (same status codes / messages) without touching a device, and write the derived
+ * configuration as "key=value" lines (lists as a,b,c; shots separated by '|') into `summary`
+ * (truncated to `capacity`).  Needs no GPU. */
+int psv_check_ini(const char *ini_path, char *summary, size_t capacity);
+
+/* CUDA device used by subsequent psv_create* calls on this thread (-1 = current device). */
+int psv_set_default_device(int device);
+int psv_device_count(int *count);
+
+/* ---- the hot path ---------------------------------------------------------------------- */
+/* fdModel::forward_simulate       src/fdModel.cpp:526-787 (binding: src/psvWave.cpp:112-158) */
+int psv_forward_simulate(psv_handle h, int i_shot, int store_fields, int verbose,
+                         int output_wavefields);
+/* fdModel::adjoint_simulate       src/fdModel.cpp:789-969 (binding: src/psvWave.cpp:160-205) */
+int psv_adjoint_simulate(psv_handle h, int i_shot, int verbose);
+/* fdModel::calculate_l2_misfit    src/fdModel.cpp:1128-1145; also stored, see PSV_REAL_MISFIT */
+int psv_calculate_l2_misfit(psv_handle h, double *misfit_out);
+/* fdModel::calculate_l2_adjoint_sources src/fdModel.cpp:1147-1162 */
+int psv_calculate_l2_adjoint_sources(psv_handle h);
+/* fdModel::reset_kernels          src/fdModel.cpp:1310-1324 */
+int psv_reset_kernels(psv_handle h);
+/* fdModel::map_kernels_to_velocity src/fdModel.cpp:1164-1183 */
+int psv_map_kernels_to_velocity(psv_handle h);
+/* fdModel::update_from_velocity   src/fdModel.cpp:1034-1051 */
+int psv_update_from_velocity(psv_handle h);
+/* fdModel::run_model              src/fdModel.cpp:1291-1308 */
+int psv_run_model(psv_handle h, int verbose, int simulate_adjoint);
+
+/* ---- model / gradient vectors (src/fdModel.cpp:1358-1515) ------------------------------- */
+int psv_get_model_vector(psv_handle h, double *out, size_t n);
+int psv_set_model_vector(psv_handle h, const double *in, size_t n);
+int psv_get_gradient_vector(psv_handle h, double *out, size_t n);
+
+/* ---- scalar attributes (read-only attributes of the Python class, src/psvWave.cpp:499-626) */
+typedef enum psv_int_key {
+  PSV_INT_NT = 0, PSV_INT_NX, PSV_INT_NZ, PSV_INT_NX_INNER, PSV_INT_NZ_INNER,
+  PSV_INT_NX_INNER_BOUNDARY, PSV_INT_NZ_INNER_BOUNDARY, PSV_INT_NP_BOUNDARY,
+  PSV_INT_N_SOURCES, PSV_INT_N_SHOTS, PSV_INT_NR, PSV_INT_SNAPSHOT_INTERVAL,
+  PSV_INT_SNAPSHOTS, PSV_INT_NX_FREE_PARAMETERS, PSV_INT_NZ_FREE_PARAMETERS,
+  PSV_INT_FREE_PARAMETERS, PSV_INT_BASIS_GRIDPOINTS_X, PSV_INT_BASIS_GRIDPOINTS_Z,
+  PSV_INT_DEVICE, PSV_INT_KEY_COUNT_
+} psv_int_key;
+typedef enum psv_real_key {
+  PSV_REAL_DX = 0, PSV_REAL_DZ, PSV_REAL_DT, PSV_REAL_NP_FACTOR, PSV_REAL_SCALAR_RHO,
+  PSV_REAL_SCALAR_VP, PSV_REAL_SCALAR_VS, PSV_REAL_PEAK_FREQUENCY, PSV_REAL_ALPHA,
+  PSV_REAL_T0, PSV_REAL_DELAY_CYCLES_PER_SHOT, PSV_REAL_MISFIT, PSV_REAL_KEY_COUNT_
+} psv_real_key;
+int psv_get_int(psv_handle h, psv_int_key key, long long *out);
+int psv_get_real(psv_handle h, psv_real_key key, double *out);
+
+/* ---- arrays ------------------------------------------------------------------------------
+ * Names follow the reference's public fields (src/fdModel.h:209-252). */
+typedef enum psv_array {
+  /* grid arrays, (nx, nz) */
+  PSV_VX = 0, PSV_VZ, PSV_TXX, PSV_TZZ, PSV_TXZ,
+  PSV_LM, PSV_LA, PSV_MU, PSV_B_VX, PSV_B_VZ, PSV_RHO, PSV_VP, PSV_VS,
+  PSV_LAMBDA_KERNEL, PSV_MU_KERNEL, PSV_DENSITY_L_KERNEL,
+  PSV_VP_KERNEL, PSV_VS_KERNEL, PSV_DENSITY_V_KERNEL, PSV_TAPER,
+  /* signals */
+  PSV_T,      /* (nt) */
+  PSV_STF,    /* (n_sources, nt) */
+  PSV_MOMENT, /* (n_sources, 2, 2) */
+  /* seismograms, (n_shots, nr, nt) */
+  PSV_RTF_UX, PSV_RTF_UZ, PSV_RTF_UX_TRUE, PSV_RTF_UZ_TRUE, PSV_A_STF_UX, PSV_A_STF_UZ,
+  /* forward snapshots, (n_shots, snapshots, nx, nz); shots never stored read as zeros */
+  PSV_ACCU_VX, PSV_ACCU_VZ, PSV_ACCU_TXX, PSV_ACCU_TZZ, PSV_ACCU_TXZ,
+  PSV_ARRAY_COUNT_
+} psv_array;
+
+int psv_array_size(psv_handle h, psv_array which, size_t *count);
+/* Copy out `count` doubles (must equal psv_array_size). */
+int psv_get_array(psv_handle h, psv_array which, double *out, size_t count);
+/* Copy in.  Settable: PSV_VP/PSV_VS/PSV_RHO (no implicit update_from_velocity),
+ * PSV_RTF_UX/UZ, PSV_RTF_UX_TRUE/UZ_TRUE, PSV_A_STF_UX/UZ, PSV_STF, PSV_MOMENT,
+ * PSV_LAMBDA_KERNEL/PSV_MU_KERNEL/PSV_DENSITY_L_KERNEL. */
+int psv_set_array(psv_handle h, psv_array which, const double *in, size_t count);
+/* fdModelExtended::set_parameter_fields (src/psvWave.cpp:256-297): copy + update_from_velocity */
+int psv_set_parameter_fields(psv_handle h, const double *vp, const double *vs, const double *rho,
+                             size_t count);
+
+typedef enum psv_index_list {
+  PSV_IX_SOURCES = 0, PSV_IZ_SOURCES, PSV_IX_RECEIVERS, PSV_IZ_RECEIVERS, /* incl. np_boundary */
+  PSV_SHOT_OFFSETS, PSV_SHOT_SOURCES
+} psv_index_list;
+int psv_index_list_size(psv_handle h, psv_index_list which, size_t *count);
+int psv_get_index_list(psv_handle h, psv_index_list which, int *out, size_t count);
+
+/* ---- text I/O next to the path (same file formats as the reference) ---------------------- */
+/* fdModel::write_receivers(prefix) src/fdModel.cpp:971-1006 */
+int psv_write_receivers(psv_handle h);
+/* fdModel::load_receivers          src/fdModel.cpp:1053-1126 */
+int psv_load_receivers(psv_handle h, int verbose);
+/* fdModel::write_sources           src/fdModel.cpp:1008-1032 */
+int psv_write_sources(psv_handle h);
+/* fdModel::write_kernels           src/fdModel.cpp:1326-1356 */
+int psv_write_kernels(psv_handle h);
+/* fdModel::load_model              src/fdModel.cpp:1185-1289 */
+int psv_load_model(psv_handle h, const char *de_path, const char *vp_path, const char *vs_path,
+                   int verbose);
+/* fdModel::load_vector             src/fdModel.cpp:1517-1572; n must be 3*nx_free*nz_free */
+int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, size_t n);
+
+/* ---- additive entry points (not in the reference) ----------------------------------------- */
+/* Drop the stored forward snapshots of one shot (i_shot >= 0) or of all shots (-1).  Lets a
+ * per-shot forward->adjoint loop run Marmousi-scale problems whose all-shots snapshot set
+ * (src/fdModel.cpp:185-190) would not fit in HBM. */
+int psv_release_snapshots(psv_handle h, int i_shot);
+/* L2 misfit of ONE shot (the terms of src/fdModel.cpp:1140-1141 for that shot only); does not
+ * touch the stored misfit.  Ranks that own a subset of the shots sum these. */
+int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out);
+/* Device pointer + element count of the three Lame-basis kernels stored back to back
+ * [lambda | mu | density_l], each nx*ld doubles with row pitch ld (see PSV_TUNE "pitch");
+ * used by the host layer for the cross-rank sum (one all-reduce) over NCCL. */
+int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count);
+int psv_synchronize(psv_handle h);
+
+/* Tuning / instrumentation knobs, by name.  Unknown names fail with PSV_ERR_INVALID_ARGUMENT.
+ *   "variant"  0 = one-thread-per-point kernels, 1 = vectorised x-marching kernels (default)
+ *   "exact"    1 = IEEE operation order of the reference (true divisions, no FMA): results
+ *              are bit-identical to the reference build; 0 (default) = reciprocals + FMA
+ *   "profile"  1 = record CUDA events around sampled stencil launches (see psv_get_stat)
+ *   "strip", "block"   launch geometry of variant 1 */
+int psv_set_option(psv_handle h, const char *name, long long value);
+int psv_get_option(psv_handle h, const char *name, long long *value);
+/* Counters of the last forward/adjoint call:
+ *   "elapsed_ms" device time of the whole time loop (CUDA events on the model's stream)
+ *   "launches"   kernels launched by that call
+ *   "stress_ms", "velocity_ms"  mean duration of one sampled launch (needs "profile" = 1)
+ *   "pitch"      row pitch (in doubles) of the device grid arrays */
+int psv_get_stat(psv_handle h, const char *name, double *value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSVWAVE_B200_H */

@@ -1,0 +1,386 @@
+// extern "C" boundary (include/psvwave_b200.h) over psv::Model.
+#include <algorithm>
+#include <cstring>
+#include <sstream>
+#include <string>
+
+#include "model.hpp"
+
+struct psv_model {
+  psv::Model *m;
+};
+
+namespace {
+thread_local std::string g_error;
+thread_local int g_default_device = -1;
+
+template <class F>
+int guarded(F &&f) {
+  try {
+    f();
+    return PSV_OK;
+  } catch (const psv::length_error &e) {
+    g_error = e.what();
+    return PSV_ERR_LENGTH;
+  } catch (const psv::invalid_argument &e) {
+    g_error = e.what();
+    return PSV_ERR_INVALID_ARGUMENT;
+  } catch (const psv::cuda_error &e) {
+    g_error = e.what();
+    return PSV_ERR_CUDA;
+  } catch (const psv::state_error &e) {
+    g_error = e.what();
+    return PSV_ERR_STATE;
+  } catch (const psv::io_error &e) {
+    g_error = e.what();
+    return PSV_ERR_IO;
+  } catch (const std::bad_alloc &) {
+    g_error = "out of host memory";
+    return PSV_ERR_LENGTH;
+  } catch (const std::exception &e) {
+    g_error = e.what();
+    return PSV_ERR_INVALID_ARGUMENT;
+  }
+}
+
+psv::Model &model(psv_handle h) {
+  if (!h || !h->m) throw psv::invalid_argument("Null psv_handle.");
+  return *h->m;
+}
+
+int pick_device() {
+  int count = 0;
+  const cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    throw psv::cuda_error(std::string("psvwave_b200 needs a CUDA device (sm_100a); none is usable: ") +
+                          (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                          ". There is no CPU fallback.");
+  }
+  int dev = g_default_device;
+  if (dev < 0) PSV_CUDA(cudaGetDevice(&dev));
+  if (dev >= count) throw psv::invalid_argument("CUDA device index out of range.");
+  return dev;
+}
+}  // namespace
+
+extern "C" {
+
+const char *psv_last_error(void) { return g_error.c_str(); }
+const char *psv_version(void) { return "psvwave_b200 0.1 (sm_100a)"; }
+
+int psv_set_default_device(int device) {
+  g_default_device = device;
+  return PSV_OK;
+}
+
+int psv_device_count(int *count) {
+  return guarded([&] {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+      cudaGetLastError();
+      n = 0;
+    }
+    *count = n;
+  });
+}
+
+int psv_create_from_ini(const char *ini_path, psv_handle *out) {
+  return guarded([&] {
+    if (!ini_path || !out) throw psv::invalid_argument("Null argument.");
+    *out = nullptr;
+    psv::Config cfg = psv::config_from_ini(ini_path);
+    const int dev = pick_device();
+    *out = new psv_model{new psv::Model(std::move(cfg), dev)};
+  });
+}
+
+int psv_check_ini(const char *ini_path, char *summary, size_t capacity) {
+  return guarded([&] {
+    if (!ini_path) throw psv::invalid_argument("Null argument.");
+    const psv::Config c = psv::config_from_ini(ini_path);
+    std::ostringstream os;
+    os.precision(17);
+    auto list = [&](const char *name, const auto &v) {
+      os << name << "=";
+      for (size_t i = 0; i < v.size(); ++i) os << (i ? "," : "") << v[i];
+      os << "\n";
+    };
+    os << "nt=" << c.nt << "\nnx_inner=" << c.nx_inner << "\nnz_inner=" << c.nz_inner
+       << "\nnx_inner_boundary=" << c.nx_inner_boundary << "\nnz_inner_boundary=" << c.nz_inner_boundary
+       << "\ndx=" << c.dx << "\ndz=" << c.dz << "\ndt=" << c.dt << "\nnp_boundary=" << c.np_boundary
+       << "\nnp_factor=" << c.np_factor << "\nscalar_rho=" << c.scalar_rho << "\nscalar_vp=" << c.scalar_vp
+       << "\nscalar_vs=" << c.scalar_vs << "\nnpx=" << c.npx << "\nnpz=" << c.npz
+       << "\npeak_frequency=" << c.peak_frequency << "\nsource_timeshift=" << c.source_timeshift
+       << "\ndelay_cycles_per_shot=" << c.delay_cycles_per_shot << "\nn_sources=" << c.n_sources
+       << "\nn_shots=" << c.n_shots << "\nnr=" << c.nr << "\nsnapshot_interval=" << c.snapshot_interval
+       << "\nnx=" << c.nx << "\nnz=" << c.nz << "\nnx_free_parameters=" << c.nx_free
+       << "\nnz_free_parameters=" << c.nz_free << "\nfree_parameters=" << c.free_parameters
+       << "\nsnapshots=" << c.snapshots << "\nobserved_data_folder=" << c.observed_data_folder
+       << "\nstf_folder=" << c.stf_folder << "\n";
+    list("ix_sources", c.ix_sources);
+    list("iz_sources", c.iz_sources);
+    list("moment_angles", c.moment_angles);
+    list("ix_receivers", c.ix_receivers);
+    list("iz_receivers", c.iz_receivers);
+    os << "which_source_to_fire_in_which_shot=";
+    for (size_t s = 0; s < c.which_source_to_fire_in_which_shot.size(); ++s) {
+      const auto &v = c.which_source_to_fire_in_which_shot[s];
+      os << (s ? "|" : "");
+      for (size_t i = 0; i < v.size(); ++i) os << (i ? "," : "") << v[i];
+    }
+    os << "\n";
+    const std::string text = os.str();
+    if (summary && capacity) {
+      const size_t n = std::min(capacity - 1, text.size());
+      std::memcpy(summary, text.data(), n);
+      summary[n] = 0;
+    }
+  });
+}
+
+int psv_create(const psv_config *c, psv_handle *out) {
+  return guarded([&] {
+    if (!c || !out) throw psv::invalid_argument("Null argument.");
+    *out = nullptr;
+    psv::Config g;
+    g.nt = c->nt;
+    g.nx_inner = c->nx_inner;
+    g.nz_inner = c->nz_inner;
+    g.nx_inner_boundary = c->nx_inner_boundary;
+    g.nz_inner_boundary = c->nz_inner_boundary;
+    g.dx = c->dx;
+    g.dz = c->dz;
+    g.dt = c->dt;
+    g.np_boundary = c->np_boundary;
+    g.np_factor = c->np_factor;
+    g.scalar_rho = c->scalar_rho;
+    g.scalar_vp = c->scalar_vp;
+    g.scalar_vs = c->scalar_vs;
+    g.npx = c->npx;
+    g.npz = c->npz;
+    g.peak_frequency = c->peak_frequency;
+    g.source_timeshift = c->source_timeshift;
+    g.delay_cycles_per_shot = c->delay_cycles_per_shot;
+    g.n_sources = c->n_sources;
+    g.n_shots = c->n_shots;
+    if (c->n_sources < 0 || c->n_shots < 0 || c->nr < 0) throw psv::invalid_argument("Negative count.");
+    if ((c->n_sources && (!c->ix_sources || !c->iz_sources || !c->moment_angles)) || !c->shot_offsets ||
+        (c->nr && (!c->ix_receivers || !c->iz_receivers)))
+      throw psv::invalid_argument("Null index list.");
+    g.ix_sources.assign(c->ix_sources, c->ix_sources + c->n_sources);
+    g.iz_sources.assign(c->iz_sources, c->iz_sources + c->n_sources);
+    g.moment_angles.assign(c->moment_angles, c->moment_angles + c->n_sources);
+    for (int s = 0; s < c->n_shots; ++s) {
+      if (c->shot_offsets[s + 1] < c->shot_offsets[s]) throw psv::invalid_argument("shot_offsets must be non-decreasing.");
+      g.which_source_to_fire_in_which_shot.emplace_back(c->shot_sources + c->shot_offsets[s],
+                                                        c->shot_sources + c->shot_offsets[s + 1]);
+    }
+    g.nr = c->nr;
+    g.ix_receivers.assign(c->ix_receivers, c->ix_receivers + c->nr);
+    g.iz_receivers.assign(c->iz_receivers, c->iz_receivers + c->nr);
+    g.snapshot_interval = c->snapshot_interval;
+    if (c->observed_data_folder) g.observed_data_folder = c->observed_data_folder;
+    if (c->stf_folder) g.stf_folder = c->stf_folder;
+    g.finalize();
+    const int dev = pick_device();
+    *out = new psv_model{new psv::Model(std::move(g), dev)};
+  });
+}
+
+int psv_clone(psv_handle src, psv_handle *out) {
+  return guarded([&] {
+    if (!out) throw psv::invalid_argument("Null argument.");
+    *out = nullptr;
+    *out = new psv_model{new psv::Model(model(src))};
+  });
+}
+
+int psv_destroy(psv_handle h) {
+  return guarded([&] {
+    if (!h) return;
+    delete h->m;
+    delete h;
+  });
+}
+
+int psv_forward_simulate(psv_handle h, int i_shot, int store_fields, int verbose, int output_wavefields) {
+  return guarded([&] { model(h).forward_simulate(i_shot, store_fields != 0, verbose != 0, output_wavefields != 0); });
+}
+int psv_adjoint_simulate(psv_handle h, int i_shot, int verbose) {
+  return guarded([&] { model(h).adjoint_simulate(i_shot, verbose != 0); });
+}
+int psv_calculate_l2_misfit(psv_handle h, double *misfit_out) {
+  return guarded([&] {
+    const double v = model(h).calculate_l2_misfit();
+    if (misfit_out) *misfit_out = v;
+  });
+}
+int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out) {
+  return guarded([&] {
+    const double v = model(h).calculate_l2_misfit_shot(i_shot);
+    if (misfit_out) *misfit_out = v;
+  });
+}
+int psv_calculate_l2_adjoint_sources(psv_handle h) {
+  return guarded([&] { model(h).calculate_l2_adjoint_sources(); });
+}
+int psv_reset_kernels(psv_handle h) {
+  return guarded([&] { model(h).reset_kernels(); });
+}
+int psv_map_kernels_to_velocity(psv_handle h) {
+  return guarded([&] { model(h).map_kernels_to_velocity(); });
+}
+int psv_update_from_velocity(psv_handle h) {
+  return guarded([&] { model(h).update_from_velocity(); });
+}
+int psv_run_model(psv_handle h, int verbose, int simulate_adjoint) {
+  return guarded([&] { model(h).run_model(verbose != 0, simulate_adjoint != 0); });
+}
+
+int psv_get_model_vector(psv_handle h, double *out, size_t n) {
+  return guarded([&] { model(h).get_model_vector(out, n); });
+}
+int psv_set_model_vector(psv_handle h, const double *in, size_t n) {
+  return guarded([&] { model(h).set_model_vector(in, n); });
+}
+int psv_get_gradient_vector(psv_handle h, double *out, size_t n) {
+  return guarded([&] { model(h).get_gradient_vector(out, n); });
+}
+
+int psv_get_int(psv_handle h, psv_int_key key, long long *out) {
+  return guarded([&] {
+    const psv::Model &m = model(h);
+    const psv::Config &c = m.config();
+    switch (key) {
+      case PSV_INT_NT: *out = c.nt; break;
+      case PSV_INT_NX: *out = c.nx; break;
+      case PSV_INT_NZ: *out = c.nz; break;
+      case PSV_INT_NX_INNER: *out = c.nx_inner; break;
+      case PSV_INT_NZ_INNER: *out = c.nz_inner; break;
+      case PSV_INT_NX_INNER_BOUNDARY: *out = c.nx_inner_boundary; break;
+      case PSV_INT_NZ_INNER_BOUNDARY: *out = c.nz_inner_boundary; break;
+      case PSV_INT_NP_BOUNDARY: *out = c.np_boundary; break;
+      case PSV_INT_N_SOURCES: *out = c.n_sources; break;
+      case PSV_INT_N_SHOTS: *out = c.n_shots; break;
+      case PSV_INT_NR: *out = c.nr; break;
+      case PSV_INT_SNAPSHOT_INTERVAL: *out = c.snapshot_interval; break;
+      case PSV_INT_SNAPSHOTS: *out = c.snapshots; break;
+      case PSV_INT_NX_FREE_PARAMETERS: *out = c.nx_free; break;
+      case PSV_INT_NZ_FREE_PARAMETERS: *out = c.nz_free; break;
+      case PSV_INT_FREE_PARAMETERS: *out = c.free_parameters; break;
+      case PSV_INT_BASIS_GRIDPOINTS_X: *out = c.npx; break;
+      case PSV_INT_BASIS_GRIDPOINTS_Z: *out = c.npz; break;
+      case PSV_INT_DEVICE: *out = m.device(); break;
+      default: throw psv::invalid_argument("Unknown integer key.");
+    }
+  });
+}
+
+int psv_get_real(psv_handle h, psv_real_key key, double *out) {
+  return guarded([&] {
+    const psv::Model &m = model(h);
+    const psv::Config &c = m.config();
+    switch (key) {
+      case PSV_REAL_DX: *out = c.dx; break;
+      case PSV_REAL_DZ: *out = c.dz; break;
+      case PSV_REAL_DT: *out = c.dt; break;
+      case PSV_REAL_NP_FACTOR: *out = c.np_factor; break;
+      case PSV_REAL_SCALAR_RHO: *out = c.scalar_rho; break;
+      case PSV_REAL_SCALAR_VP: *out = c.scalar_vp; break;
+      case PSV_REAL_SCALAR_VS: *out = c.scalar_vs; break;
+      case PSV_REAL_PEAK_FREQUENCY: *out = c.peak_frequency; break;
+      case PSV_REAL_ALPHA: *out = c.alpha; break;
+      case PSV_REAL_T0: *out = c.source_timeshift; break;
+      case PSV_REAL_DELAY_CYCLES_PER_SHOT: *out = c.delay_cycles_per_shot; break;
+      case PSV_REAL_MISFIT: *out = m.misfit(); break;
+      default: throw psv::invalid_argument("Unknown real key.");
+    }
+  });
+}
+
+int psv_array_size(psv_handle h, psv_array which, size_t *count) {
+  return guarded([&] { *count = model(h).array_size(which); });
+}
+int psv_get_array(psv_handle h, psv_array which, double *out, size_t count) {
+  return guarded([&] { model(h).get_array(which, out, count); });
+}
+int psv_set_array(psv_handle h, psv_array which, const double *in, size_t count) {
+  return guarded([&] { model(h).set_array(which, in, count); });
+}
+int psv_set_parameter_fields(psv_handle h, const double *vp, const double *vs, const double *rho, size_t count) {
+  return guarded([&] { model(h).set_parameter_fields(vp, vs, rho, count); });
+}
+
+namespace {
+std::vector<int> index_list(const psv::Config &c, psv_index_list which) {
+  switch (which) {
+    case PSV_IX_SOURCES: return c.ix_sources;
+    case PSV_IZ_SOURCES: return c.iz_sources;
+    case PSV_IX_RECEIVERS: return c.ix_receivers;
+    case PSV_IZ_RECEIVERS: return c.iz_receivers;
+    case PSV_SHOT_OFFSETS: {
+      std::vector<int> off(1, 0);
+      for (const auto &s : c.which_source_to_fire_in_which_shot) off.push_back(off.back() + (int)s.size());
+      return off;
+    }
+    case PSV_SHOT_SOURCES: {
+      std::vector<int> flat;
+      for (const auto &s : c.which_source_to_fire_in_which_shot) flat.insert(flat.end(), s.begin(), s.end());
+      return flat;
+    }
+  }
+  throw psv::invalid_argument("Unknown index list.");
+}
+}  // namespace
+
+int psv_index_list_size(psv_handle h, psv_index_list which, size_t *count) {
+  return guarded([&] { *count = index_list(model(h).config(), which).size(); });
+}
+int psv_get_index_list(psv_handle h, psv_index_list which, int *out, size_t count) {
+  return guarded([&] {
+    const std::vector<int> v = index_list(model(h).config(), which);
+    if (count != v.size()) throw psv::invalid_argument("Index list size mismatch.");
+    if (count) std::memcpy(out, v.data(), count * sizeof(int));
+  });
+}
+
+int psv_write_receivers(psv_handle h) {
+  return guarded([&] { model(h).write_receivers(); });
+}
+int psv_load_receivers(psv_handle h, int verbose) {
+  return guarded([&] { model(h).load_receivers(verbose != 0); });
+}
+int psv_write_sources(psv_handle h) {
+  return guarded([&] { model(h).write_sources(); });
+}
+int psv_write_kernels(psv_handle h) {
+  return guarded([&] { model(h).write_kernels(); });
+}
+int psv_load_model(psv_handle h, const char *de_path, const char *vp_path, const char *vs_path, int verbose) {
+  return guarded([&] { model(h).load_model(de_path, vp_path, vs_path, verbose != 0); });
+}
+int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, size_t n) {
+  return guarded([&] { model(h).load_vector(path, verbose != 0, out, n); });
+}
+
+int psv_release_snapshots(psv_handle h, int i_shot) {
+  return guarded([&] { model(h).release_snapshots(i_shot); });
+}
+int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count) {
+  return guarded([&] { model(h).kernel_buffer(device_ptr, count); });
+}
+int psv_synchronize(psv_handle h) {
+  return guarded([&] { model(h).synchronize(); });
+}
+int psv_set_option(psv_handle h, const char *name, long long value) {
+  return guarded([&] { model(h).set_option(name, value); });
+}
+int psv_get_option(psv_handle h, const char *name, long long *value) {
+  return guarded([&] { *value = model(h).get_option(name); });
+}
+int psv_get_stat(psv_handle h, const char *name, double *value) {
+  return guarded([&] { *value = model(h).get_stat(name); });
+}
+
+}  // extern "C"

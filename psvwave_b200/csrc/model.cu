@@ -1,0 +1,1032 @@
+#include "model.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <limits>
+#include <sstream>
+
+#include "kernels.cuh"
+#include "pointwise.cuh"
+
+namespace psv {
+
+void cuda_check(cudaError_t e, const char *what, const char *file, int line) {
+  if (e == cudaSuccess) return;
+  std::ostringstream os;
+  os << "CUDA error '" << cudaGetErrorString(e) << "' in " << what << " (" << file << ":" << line << ")";
+  throw cuda_error(os.str());
+}
+
+void DeviceBuffer::allocate(size_t bytes) {
+  release();
+  if (bytes == 0) bytes = 8;
+  PSV_CUDA(cudaMalloc(&p_, bytes));
+  bytes_ = bytes;
+  PSV_CUDA(cudaMemset(p_, 0, bytes));
+}
+
+void DeviceBuffer::release() {
+  if (p_) cudaFree(p_);
+  p_ = nullptr;
+  bytes_ = 0;
+}
+
+namespace {
+constexpr double kPiTruncated = 3.14159265;  // the reference's PI macro (src/fdModel.cpp:14)
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline unsigned blocks_for(size_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+std::string zero_pad(int v, int width) {
+  std::ostringstream os;
+  os << std::setw(width) << std::setfill('0') << v;
+  return os.str();
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// construction
+// ---------------------------------------------------------------------------------------------
+Model::Model(Config cfg, int device) : cfg_(std::move(cfg)), device_(device) {
+  bind();
+  PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  PSV_CUDA(cudaEventCreate(&ev_begin_));
+  PSV_CUDA(cudaEventCreate(&ev_end_));
+  allocate();
+  initialize_host_tables();
+  build_plans();
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+Model::~Model() {
+  cudaSetDevice(device_);
+  for (cudaEvent_t e : prof_events_) cudaEventDestroy(e);
+  if (ev_begin_) cudaEventDestroy(ev_begin_);
+  if (ev_end_) cudaEventDestroy(ev_end_);
+  if (stream_) cudaStreamDestroy(stream_);
+}
+
+void Model::bind() const { PSV_CUDA(cudaSetDevice(device_)); }
+
+GridArray Model::make_grid() const {
+  GridArray g;
+  g.guard = guard_;
+  g.buf.allocate((grid_elems_ + 2 * guard_) * sizeof(double));
+  return g;
+}
+
+void Model::allocate() {
+  const Config &c = cfg_;
+  ld_ = round_up(c.nz, 16);
+  grid_elems_ = (size_t)c.nx * ld_;
+  guard_ = 2 * (size_t)ld_ + 16;
+  n_snap_alloc_ = (c.nt + c.snapshot_interval - 1) / c.snapshot_interval;
+
+  GridArray *grids[] = {&vx_, &vz_, &txx_, &tzz_, &txz_, &vp_, &vs_, &rho_, &lm_, &mu_, &b_,
+                        &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  for (GridArray *g : grids) *g = make_grid();
+  lame_kernels_.allocate(3 * grid_elems_ * sizeof(double));
+  taper_table_.allocate((c.np_boundary + 1) * sizeof(double));
+  stf_.allocate((size_t)c.n_sources * c.nt * sizeof(double));
+  const size_t rec = (size_t)c.n_shots * c.nr * c.nt * sizeof(double);
+  DeviceBuffer *recs[] = {&rtf_ux_, &rtf_uz_, &obs_ux_, &obs_uz_, &a_stf_ux_, &a_stf_uz_};
+  for (DeviceBuffer *b : recs) b->allocate(rec);
+  snapshots_.resize(c.n_shots);
+  plans_.resize(c.n_shots);
+}
+
+void Model::initialize_host_tables() {
+  const Config &c = cfg_;
+  const int nt = c.nt;
+  // time axis and Ricker wavelets (src/fdModel.cpp:215-231); the delay of a source is its
+  // position inside its shot's list times delay_cycles_per_shot periods.
+  t_host_.assign(nt, 0.0);
+  stf_host_.assign((size_t)c.n_sources * nt, 0.0);
+  for (int shot = 0; shot < c.n_shots; ++shot) {
+    const std::vector<int> &list = c.which_source_to_fire_in_which_shot[shot];
+    for (int k = 0; k < (int)list.size(); ++k) {
+      for (unsigned int it = 0; it < (unsigned int)nt; ++it) {
+        t_host_[it] = it * c.dt;
+        const double f = 1.0 / c.alpha;
+        const double tau = t_host_[it] - 1.4 / f - c.delay_cycles_per_shot * k / f;
+        stf_host_[(size_t)list[k] * nt + it] =
+            (1 - 2 * std::pow(M_PI * f * tau, 2)) * std::exp(-std::pow(M_PI * f * tau, 2));
+      }
+    }
+  }
+  PSV_CUDA(cudaMemcpy(stf_.as<>(), stf_host_.data(), stf_host_.size() * sizeof(double),
+                      cudaMemcpyHostToDevice));
+  // moment tensors (src/fdModel.cpp:234-246)
+  moment_host_.assign((size_t)c.n_sources * 4, 0.0);
+  for (int s = 0; s < c.n_sources; ++s) {
+    const double ang = c.moment_angles[s];
+    moment_host_[s * 4 + 0] = std::cos(ang * kPiTruncated / 180.0) * 1e15;
+    moment_host_[s * 4 + 1] = -std::sin(ang * kPiTruncated / 180.0) * 1e15;
+    moment_host_[s * 4 + 2] = -std::sin(ang * kPiTruncated / 180.0) * 1e15;
+    moment_host_[s * 4 + 3] = -std::cos(ang * kPiTruncated / 180.0) * 1e15;
+  }
+  // taper table (src/fdModel.cpp:263-298): value for `n` enclosing frames, n = 0..np
+  taper_host_.assign(c.np_boundary + 1, 1.0);
+  for (int n = 0; n <= c.np_boundary; ++n) {
+    const double cnt = (double)n;
+    taper_host_[n] = std::exp(-std::pow(c.np_factor * (c.np_boundary - cnt), 2));
+  }
+  PSV_CUDA(cudaMemcpy(taper_table_.as<>(), taper_host_.data(), taper_host_.size() * sizeof(double),
+                      cudaMemcpyHostToDevice));
+  // homogeneous medium (src/fdModel.cpp:249-261); pad columns get the same values so that
+  // 1/rho stays finite everywhere.
+  std::vector<double> fill(grid_elems_);
+  const std::pair<GridArray *, double> scal[] = {{&vp_, c.scalar_vp}, {&vs_, c.scalar_vs}, {&rho_, c.scalar_rho}};
+  for (const auto &p : scal) {
+    std::fill(fill.begin(), fill.end(), p.second);
+    PSV_CUDA(cudaMemcpy(p.first->data(), fill.data(), grid_elems_ * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  update_from_velocity();
+}
+
+void Model::build_plans() {
+  const Config &c = cfg_;
+  // receivers: linear index + chains of receivers sharing a grid point
+  std::vector<int> idx(std::max(c.nr, 1), 0), next(std::max(c.nr, 1), -1), heads;
+  std::map<int, int> last;
+  for (int r = 0; r < c.nr; ++r) {
+    idx[r] = c.ix_receivers[r] * ld_ + c.iz_receivers[r];
+    auto it = last.find(idx[r]);
+    if (it == last.end()) heads.push_back(r);
+    else next[it->second] = r;
+    last[idx[r]] = r;
+  }
+  n_rec_heads_ = (int)heads.size();
+  if (heads.empty()) heads.push_back(0);
+  rec_index_.allocate(idx.size() * sizeof(int));
+  rec_next_.allocate(next.size() * sizeof(int));
+  rec_heads_.allocate(heads.size() * sizeof(int));
+  PSV_CUDA(cudaMemcpy(rec_index_.as<int>(), idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+  PSV_CUDA(cudaMemcpy(rec_next_.as<int>(), next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice));
+  PSV_CUDA(cudaMemcpy(rec_heads_.as<int>(), heads.data(), heads.size() * sizeof(int), cudaMemcpyHostToDevice));
+
+  // sources: the 12 point updates per source in the order of src/fdModel.cpp:702-750
+  const double dx4 = c.dx * c.dx * c.dx * c.dx, dz4 = c.dz * c.dz * c.dz * c.dz;
+  for (int shot = 0; shot < c.n_shots; ++shot) {
+    std::vector<InjectOp> ops;
+    std::vector<int> op_heads;
+    std::map<std::pair<int, int>, int> last_op;
+    auto push = [&](int field, int x, int z, int source, double weight, double sign, double d4) {
+      InjectOp op;
+      op.point = x * ld_ + z;
+      op.field = field;
+      op.source = source;
+      op.next = -1;
+      op.weight = weight;
+      op.sign = sign;
+      op.d4 = d4;
+      const int id = (int)ops.size();
+      const auto key = std::make_pair(field, op.point);
+      auto it = last_op.find(key);
+      if (it == last_op.end()) op_heads.push_back(id);
+      else ops[it->second].next = id;
+      last_op[key] = id;
+      ops.push_back(op);
+    };
+    for (int s : c.which_source_to_fire_in_which_shot[shot]) {
+      const int x = c.ix_sources[s], z = c.iz_sources[s];
+      const double *M = &moment_host_[(size_t)s * 4];
+      push(0, x - 1, z, s, M[0], -1, dx4);             // (x,x)
+      push(0, x, z, s, M[0], +1, dx4);
+      push(1, x, z - 1, s, M[3], -1, dz4);             // (z,z)
+      push(1, x, z, s, M[3], +1, dz4);
+      push(0, x - 1, z + 1, s, 0.25 * M[1], +1, dx4);  // (x,z)
+      push(0, x, z + 1, s, 0.25 * M[1], +1, dx4);
+      push(0, x - 1, z - 1, s, 0.25 * M[1], -1, dx4);
+      push(0, x, z - 1, s, 0.25 * M[1], -1, dx4);
+      push(1, x + 1, z - 1, s, 0.25 * M[2], +1, dz4);  // (z,x)
+      push(1, x + 1, z, s, 0.25 * M[2], +1, dz4);
+      push(1, x - 1, z - 1, s, 0.25 * M[2], -1, dz4);
+      push(1, x - 1, z, s, 0.25 * M[2], -1, dz4);
+    }
+    ShotPlan &p = plans_[shot];
+    p.n_heads = (int)op_heads.size();
+    if (ops.empty()) continue;
+    p.ops.allocate(ops.size() * sizeof(InjectOp));
+    p.heads.allocate(op_heads.size() * sizeof(int));
+    PSV_CUDA(cudaMemcpy(p.ops.as<InjectOp>(), ops.data(), ops.size() * sizeof(InjectOp), cudaMemcpyHostToDevice));
+    PSV_CUDA(cudaMemcpy(p.heads.as<int>(), op_heads.data(), op_heads.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+}
+
+// Deep copy: every array, the stored snapshots included (src/fdModel.cpp:301-388).
+Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
+  bind();
+  PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  PSV_CUDA(cudaEventCreate(&ev_begin_));
+  PSV_CUDA(cudaEventCreate(&ev_end_));
+  allocate();
+  t_host_ = o.t_host_;
+  stf_host_ = o.stf_host_;
+  moment_host_ = o.moment_host_;
+  taper_host_ = o.taper_host_;
+  misfit_ = o.misfit_;
+  variant_ = o.variant_;
+  exact_ = o.exact_;
+  profile_ = o.profile_;
+  strip_ = o.strip_;
+  block_ = o.block_;
+  PSV_CUDA(cudaStreamSynchronize(o.stream_));
+  auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
+    if (src.empty()) return;
+    if (dst.bytes() != src.bytes()) dst.allocate(src.bytes());
+    PSV_CUDA(cudaMemcpy(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice));
+  };
+  const GridArray *gs[] = {&o.vx_, &o.vz_, &o.txx_, &o.tzz_, &o.txz_, &o.vp_, &o.vs_, &o.rho_, &o.lm_,
+                           &o.mu_, &o.b_, &o.vp_kernel_, &o.vs_kernel_, &o.density_v_kernel_};
+  GridArray *gd[] = {&vx_, &vz_, &txx_, &tzz_, &txz_, &vp_, &vs_, &rho_, &lm_,
+                     &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  for (size_t i = 0; i < sizeof(gs) / sizeof(gs[0]); ++i) dcopy(gs[i]->buf, gd[i]->buf);
+  dcopy(o.lame_kernels_, lame_kernels_);
+  dcopy(o.taper_table_, taper_table_);
+  dcopy(o.stf_, stf_);
+  dcopy(o.rtf_ux_, rtf_ux_);
+  dcopy(o.rtf_uz_, rtf_uz_);
+  dcopy(o.obs_ux_, obs_ux_);
+  dcopy(o.obs_uz_, obs_uz_);
+  dcopy(o.a_stf_ux_, a_stf_ux_);
+  dcopy(o.a_stf_uz_, a_stf_uz_);
+  for (int s = 0; s < cfg_.n_shots; ++s) dcopy(o.snapshots_[s], snapshots_[s]);
+  build_plans();
+  PSV_CUDA(cudaDeviceSynchronize());
+}
+
+// ---------------------------------------------------------------------------------------------
+// host <-> device helpers
+// ---------------------------------------------------------------------------------------------
+void Model::grid_to_host(const double *dev, double *host) const {
+  PSV_CUDA(cudaMemcpy2D(host, cfg_.nz * sizeof(double), dev, ld_ * sizeof(double),
+                        cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyDeviceToHost));
+}
+
+void Model::grid_from_host(double *dev, const double *host) const {
+  PSV_CUDA(cudaMemcpy2D(dev, ld_ * sizeof(double), host, cfg_.nz * sizeof(double),
+                        cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyHostToDevice));
+}
+
+void Model::synchronize() {
+  bind();
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::check_shot(int i_shot) const {
+  if (i_shot < 0 || i_shot >= cfg_.n_shots) throw invalid_argument("Shot index out of range.");
+}
+
+void Model::zero_dynamic_fields() {
+  GridArray *f[] = {&vx_, &vz_, &txx_, &tzz_, &txz_};
+  for (GridArray *g : f) PSV_CUDA(cudaMemsetAsync(g->buf.as<char>(), 0, g->buf.bytes(), stream_));
+}
+
+void Model::ensure_snapshots(int i_shot) {
+  DeviceBuffer &s = snapshots_[i_shot];
+  const size_t bytes = 5 * (size_t)n_snap_alloc_ * grid_elems_ * sizeof(double);
+  if (s.empty()) {
+    try {
+      s.allocate(bytes);
+    } catch (const cuda_error &e) {
+      cudaGetLastError();
+      std::ostringstream os;
+      os << "Cannot keep the forward snapshots of shot " << i_shot << " in device memory ("
+         << (bytes >> 20) << " MiB: 5 fields x " << n_snap_alloc_ << " snapshots x " << cfg_.nx << "x"
+         << cfg_.nz << "). Release other shots with psv_release_snapshots / run shots one at a time. ["
+         << e.what() << "]";
+      throw length_error(os.str());
+    }
+  }
+}
+
+double *Model::snapshot_ptr(int i_shot, int field, int snap) const {
+  return snapshots_[i_shot].as<double>() + ((size_t)field * n_snap_alloc_ + snap) * grid_elems_;
+}
+
+void Model::release_snapshots(int i_shot) {
+  bind();
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  if (i_shot < 0) {
+    for (DeviceBuffer &s : snapshots_) s.release();
+  } else {
+    check_shot(i_shot);
+    snapshots_[i_shot].release();
+  }
+}
+
+void Model::kernel_buffer(void **ptr, size_t *count) const {
+  *ptr = lame_kernels_.as<double>();
+  *count = 3 * grid_elems_;
+}
+
+// ---------------------------------------------------------------------------------------------
+// sweeps
+// ---------------------------------------------------------------------------------------------
+namespace {
+template <class M, int MODE>
+void launch_stress_t(int variant, const StressArgs &a, int block, cudaStream_t st) {
+  if (variant == 0) {
+    dim3 grid((a.g.nz + 31) / 32, (a.g.nx + 7) / 8), blk(32, 8);
+    stress_point_kernel<M, MODE><<<grid, blk, 0, st>>>(a);
+  } else {
+    const int pairs = a.g.ld / 2;
+    dim3 grid((pairs + block - 1) / block, (a.g.nx + a.strip - 1) / a.strip), blk(block);
+    stress_march_kernel<M, MODE><<<grid, blk, 0, st>>>(a);
+  }
+}
+template <class M>
+void launch_stress_m(int variant, int mode, const StressArgs &a, int block, cudaStream_t st) {
+  if (mode == MODE_SNAPSHOT) launch_stress_t<M, MODE_SNAPSHOT>(variant, a, block, st);
+  else if (mode == MODE_ACCUMULATE) launch_stress_t<M, MODE_ACCUMULATE>(variant, a, block, st);
+  else launch_stress_t<M, MODE_PLAIN>(variant, a, block, st);
+}
+template <class M>
+void launch_velocity_t(int variant, const VelocityArgs &a, int block, cudaStream_t st) {
+  if (variant == 0) {
+    dim3 grid((a.g.nz + 31) / 32, (a.g.nx + 7) / 8), blk(32, 8);
+    velocity_point_kernel<M><<<grid, blk, 0, st>>>(a);
+  } else {
+    const int pairs = a.g.ld / 2;
+    dim3 grid((pairs + block - 1) / block, (a.g.nx + a.strip - 1) / a.strip), blk(block);
+    velocity_march_kernel<M><<<grid, blk, 0, st>>>(a);
+  }
+}
+}  // namespace
+
+void Model::launch_stress(double sdt, int mode, int i_shot, int snap) {
+  const Config &c = cfg_;
+  StressArgs a{};
+  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
+  a.vx = vx_.data();
+  a.vz = vz_.data();
+  a.txx = txx_.data();
+  a.tzz = tzz_.data();
+  a.txz = txz_.data();
+  a.lm = lm_.data();
+  a.mu = mu_.data();
+  a.taper_table = taper_table_.as<>();
+  if (mode != MODE_PLAIN) {
+    a.s_vx = snapshot_ptr(i_shot, 0, snap);
+    a.s_vz = snapshot_ptr(i_shot, 1, snap);
+    a.s_txx = snapshot_ptr(i_shot, 2, snap);
+    a.s_tzz = snapshot_ptr(i_shot, 3, snap);
+    a.s_txz = snapshot_ptr(i_shot, 4, snap);
+  }
+  if (mode == MODE_ACCUMULATE) {
+    a.k_lam = lame_kernels_.as<double>();
+    a.k_mu = lame_kernels_.as<double>() + grid_elems_;
+    a.k_rho = lame_kernels_.as<double>() + 2 * grid_elems_;
+    a.wx0 = c.np_boundary + c.nx_inner_boundary;
+    a.wx1 = c.np_boundary + c.nx_inner - c.nx_inner_boundary;
+    a.wz0 = c.np_boundary + c.nz_inner_boundary;
+    a.wz1 = c.np_boundary + c.nz_inner - c.nz_inner_boundary;
+    a.sidt = c.snapshot_interval * c.dt;
+  }
+  a.strip = strip_;
+  if (exact_) launch_stress_m<ExactMath>(variant_, mode, a, block_, stream_);
+  else launch_stress_m<FastMath>(variant_, mode, a, block_, stream_);
+  ++stat_launches_;
+}
+
+void Model::launch_velocity(double sdt) {
+  const Config &c = cfg_;
+  VelocityArgs a{};
+  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
+  a.txx = txx_.data();
+  a.tzz = tzz_.data();
+  a.txz = txz_.data();
+  a.vx = vx_.data();
+  a.vz = vz_.data();
+  a.b = b_.data();
+  a.taper_table = taper_table_.as<>();
+  a.strip = strip_;
+  if (exact_) launch_velocity_t<ExactMath>(variant_, a, block_, stream_);
+  else launch_velocity_t<FastMath>(variant_, a, block_, stream_);
+  ++stat_launches_;
+}
+
+namespace {
+struct Profiler {  // CUDA events around sampled sweep launches
+  std::vector<cudaEvent_t> &ev;
+  cudaStream_t st;
+  bool on;
+  int every, n = 0;
+  Profiler(std::vector<cudaEvent_t> &e, cudaStream_t s, bool enabled, int nt)
+      : ev(e), st(s), on(enabled), every(std::max(1, nt / 32)) {
+    if (on && ev.empty()) {
+      ev.resize(3 * 40);
+      for (cudaEvent_t &x : ev) PSV_CUDA(cudaEventCreate(&x));
+    }
+  }
+  bool sample(int it) const { return on && it % every == 0 && 3 * (n + 1) <= (int)ev.size(); }
+  void mark(int k) { PSV_CUDA(cudaEventRecord(ev[3 * n + k], st)); }
+  void next() { ++n; }
+  void collect(double &stress_ms, double &velocity_ms) {
+    stress_ms = velocity_ms = 0;
+    if (!on || n == 0) return;
+    for (int i = 0; i < n; ++i) {
+      float a = 0, b = 0;
+      PSV_CUDA(cudaEventElapsedTime(&a, ev[3 * i], ev[3 * i + 1]));
+      PSV_CUDA(cudaEventElapsedTime(&b, ev[3 * i + 1], ev[3 * i + 2]));
+      stress_ms += a;
+      velocity_ms += b;
+    }
+    stress_ms /= n;
+    velocity_ms /= n;
+  }
+};
+}  // namespace
+
+// fdModel::forward_simulate (src/fdModel.cpp:526-787)
+void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool output_wavefields) {
+  check_shot(i_shot);
+  bind();
+  const Config &c = cfg_;
+  if (store_fields) ensure_snapshots(i_shot);
+  const auto wall0 = std::chrono::steady_clock::now();
+  stat_launches_ = 0;
+  zero_dynamic_fields();
+  PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+  Profiler prof(prof_events_, stream_, profile_, c.nt);
+
+  const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
+  RecordArgs ra{vx_.data(), vz_.data(), rec_index_.as<int>(), rtf_ux_.as<>() + shot_rows,
+                rtf_uz_.as<>() + shot_rows, c.nr, c.nt, 0, c.dt, c.dx * c.dz};
+  const ShotPlan &plan = plans_[i_shot];
+  InjectArgs ia{vx_.data(), vz_.data(), b_.data(), stf_.as<>(), plan.ops.as<InjectOp>(),
+                plan.heads.as<int>(), plan.n_heads, c.nt, 0, c.dt};
+
+  for (int it = 0; it < c.nt; ++it) {
+    if (c.nr > 0) {
+      ra.it = it;
+      record_receivers_kernel<<<blocks_for(c.nr, 128), 128, 0, stream_>>>(ra);
+      ++stat_launches_;
+    }
+    const bool snap = store_fields && it % c.snapshot_interval == 0;
+    const bool sample = prof.sample(it);
+    if (sample) prof.mark(0);
+    launch_stress(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, i_shot, it / c.snapshot_interval);
+    if (sample) prof.mark(1);
+    launch_velocity(c.dt);
+    if (sample) {
+      prof.mark(2);
+      prof.next();
+    }
+    if (plan.n_heads > 0) {
+      ia.it = it;
+      inject_sources_kernel<<<blocks_for(plan.n_heads, 64), 64, 0, stream_>>>(ia);
+      ++stat_launches_;
+    }
+    if (output_wavefields && it % 10 == 0) write_wavefield_files(it);
+  }
+  PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  float ms = 0;
+  PSV_CUDA(cudaEventElapsedTime(&ms, ev_begin_, ev_end_));
+  stat_elapsed_ms_ = ms;
+  prof.collect(stat_stress_ms_, stat_velocity_ms_);
+  if (verbose) {
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+    std::cout << "Seconds elapsed for forward wave simulation: " << secs << std::endl;
+  }
+}
+
+// fdModel::adjoint_simulate (src/fdModel.cpp:789-969)
+void Model::adjoint_simulate(int i_shot, bool verbose) {
+  check_shot(i_shot);
+  bind();
+  const Config &c = cfg_;
+  if (snapshots_[i_shot].empty())
+    throw state_error("adjoint_simulate needs the forward wavefield of this shot: call "
+                      "forward_simulate(i_shot, store_fields=True) first.");
+  const auto wall0 = std::chrono::steady_clock::now();
+  stat_launches_ = 0;
+  zero_dynamic_fields();
+  PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+  Profiler prof(prof_events_, stream_, profile_, c.nt);
+
+  const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
+  AdjointInjectArgs aa{vx_.data(), vz_.data(), b_.data(), a_stf_ux_.as<>() + shot_rows,
+                       a_stf_uz_.as<>() + shot_rows, rec_index_.as<int>(), rec_next_.as<int>(),
+                       rec_heads_.as<int>(), n_rec_heads_, c.nt, 0, c.dt, c.dx * c.dz};
+  for (int it = c.nt - 1; it >= 0; --it) {
+    const bool corr = it % c.snapshot_interval == 0;
+    const bool sample = prof.sample(it);
+    if (sample) prof.mark(0);
+    launch_stress(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, i_shot, it / c.snapshot_interval);
+    if (sample) prof.mark(1);
+    launch_velocity(-c.dt);
+    if (sample) {
+      prof.mark(2);
+      prof.next();
+    }
+    if (n_rec_heads_ > 0) {
+      aa.it = it;
+      inject_adjoint_kernel<<<blocks_for(n_rec_heads_, 128), 128, 0, stream_>>>(aa);
+      ++stat_launches_;
+    }
+  }
+  PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  float ms = 0;
+  PSV_CUDA(cudaEventElapsedTime(&ms, ev_begin_, ev_end_));
+  stat_elapsed_ms_ = ms;
+  prof.collect(stat_stress_ms_, stat_velocity_ms_);
+  if (verbose) {
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+    std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
+  }
+}
+
+// fdModel::run_model (src/fdModel.cpp:1291-1308)
+void Model::run_model(bool verbose, bool simulate_adjoint) {
+  for (int s = 0; s < cfg_.n_shots; ++s) forward_simulate(s, true, verbose, false);
+  calculate_l2_misfit();
+  if (simulate_adjoint) {
+    calculate_l2_adjoint_sources();
+    reset_kernels();
+    for (int s = 0; s < cfg_.n_shots; ++s) adjoint_simulate(s, verbose);
+    map_kernels_to_velocity();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// point-wise stages
+// ---------------------------------------------------------------------------------------------
+void Model::update_from_velocity() {
+  bind();
+  update_from_velocity_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(
+      vp_.data(), vs_.data(), rho_.data(), lm_.data(), mu_.data(), b_.data(), grid_elems_);
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+double Model::misfit_of_range(size_t first, size_t n) {
+  bind();
+  const size_t per_block = (size_t)kMisfitThreads * kMisfitPerThread;
+  const unsigned nb = (unsigned)std::max<size_t>(1, (n + per_block - 1) / per_block);
+  if (scratch_.bytes() < nb * sizeof(double)) scratch_.allocate(nb * sizeof(double));
+  misfit_partial_kernel<<<nb, kMisfitThreads, 0, stream_>>>(rtf_ux_.as<>() + first, rtf_uz_.as<>() + first,
+                                                            obs_ux_.as<>() + first, obs_uz_.as<>() + first, n,
+                                                            0.5 * cfg_.dt, scratch_.as<>());
+  PSV_CUDA(cudaGetLastError());
+  std::vector<double> partial(nb);
+  PSV_CUDA(cudaMemcpyAsync(partial.data(), scratch_.as<>(), nb * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  double acc = 0.0;
+  for (double p : partial) acc += p;
+  return acc;
+}
+
+double Model::calculate_l2_misfit() {
+  misfit_ = misfit_of_range(0, (size_t)cfg_.n_shots * cfg_.nr * cfg_.nt);
+  return misfit_;
+}
+
+double Model::calculate_l2_misfit_shot(int i_shot) {
+  check_shot(i_shot);
+  const size_t per_shot = (size_t)cfg_.nr * cfg_.nt;
+  return misfit_of_range((size_t)i_shot * per_shot, per_shot);
+}
+
+void Model::calculate_l2_adjoint_sources() {
+  bind();
+  const size_t n = (size_t)cfg_.n_shots * cfg_.nr * cfg_.nt;
+  if (n == 0) return;
+  adjoint_sources_kernel<<<blocks_for(n, 256), 256, 0, stream_>>>(rtf_ux_.as<>(), rtf_uz_.as<>(), obs_ux_.as<>(),
+                                                                  obs_uz_.as<>(), a_stf_ux_.as<>(),
+                                                                  a_stf_uz_.as<>(), n);
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::reset_kernels() {
+  bind();
+  PSV_CUDA(cudaMemsetAsync(lame_kernels_.as<char>(), 0, lame_kernels_.bytes(), stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::map_kernels_to_velocity() {
+  bind();
+  double *k = lame_kernels_.as<double>();
+  map_kernels_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(
+      vp_.data(), vs_.data(), b_.data(), k, k + grid_elems_, k + 2 * grid_elems_, vp_kernel_.data(),
+      vs_kernel_.data(), density_v_kernel_.data(), grid_elems_);
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+// ---------------------------------------------------------------------------------------------
+// model / gradient vectors
+// ---------------------------------------------------------------------------------------------
+namespace {
+VectorArgs vector_args(const Config &c, int ld) {
+  VectorArgs a;
+  a.npx = c.npx;
+  a.npz = c.npz;
+  a.nbx = c.nx_free / c.npx;
+  a.nbz = c.nz_free / c.npz;
+  a.x0 = c.nx_inner_boundary + c.np_boundary;
+  a.z0 = c.nz_inner_boundary + c.np_boundary;
+  a.ld = ld;
+  a.per = (size_t)a.nbx * a.nbz;
+  return a;
+}
+}  // namespace
+
+void Model::get_model_vector(double *out, size_t n) {
+  bind();
+  if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Model vector has the wrong length.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
+  vector_kernel<VEC_MEAN><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(),
+                                                                       scratch_.as<>());
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaMemcpyAsync(out, scratch_.as<>(), n * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::set_model_vector(const double *in, size_t n) {
+  bind();
+  if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Model vector has the wrong length.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
+  PSV_CUDA(cudaMemcpyAsync(scratch_.as<>(), in, n * sizeof(double), cudaMemcpyHostToDevice, stream_));
+  vector_kernel<VEC_FILL><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(),
+                                                                       scratch_.as<>());
+  PSV_CUDA(cudaGetLastError());
+  update_from_velocity();  // src/fdModel.cpp:1456
+}
+
+void Model::get_gradient_vector(double *out, size_t n) {
+  bind();
+  if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Gradient vector has the wrong length.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
+  vector_kernel<VEC_SUM><<<blocks_for(a.per, 128), 128, 0, stream_>>>(
+      a, vp_kernel_.data(), vs_kernel_.data(), density_v_kernel_.data(), scratch_.as<>());
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaMemcpyAsync(out, scratch_.as<>(), n * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+// ---------------------------------------------------------------------------------------------
+// arrays in / out
+// ---------------------------------------------------------------------------------------------
+size_t Model::array_size(psv_array which) const {
+  const Config &c = cfg_;
+  const size_t grid = (size_t)c.nx * c.nz;
+  if (which >= PSV_VX && which <= PSV_TAPER) return grid;
+  if (which == PSV_T) return c.nt;
+  if (which == PSV_STF) return (size_t)c.n_sources * c.nt;
+  if (which == PSV_MOMENT) return (size_t)c.n_sources * 4;
+  if (which >= PSV_RTF_UX && which <= PSV_A_STF_UZ) return (size_t)c.n_shots * c.nr * c.nt;
+  if (which >= PSV_ACCU_VX && which <= PSV_ACCU_TXZ) return (size_t)c.n_shots * c.snapshots * grid;
+  throw invalid_argument("Unknown array id.");
+}
+
+void Model::get_array(psv_array which, double *out, size_t count) {
+  bind();
+  if (count != array_size(which)) throw invalid_argument("Array size mismatch.");
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  const Config &c = cfg_;
+  const size_t grid = (size_t)c.nx * c.nz;
+  double *k = lame_kernels_.as<double>();
+  switch (which) {
+    case PSV_VX: return grid_to_host(vx_.data(), out);
+    case PSV_VZ: return grid_to_host(vz_.data(), out);
+    case PSV_TXX: return grid_to_host(txx_.data(), out);
+    case PSV_TZZ: return grid_to_host(tzz_.data(), out);
+    case PSV_TXZ: return grid_to_host(txz_.data(), out);
+    case PSV_LM: return grid_to_host(lm_.data(), out);
+    case PSV_MU: return grid_to_host(mu_.data(), out);
+    case PSV_B_VX:
+    case PSV_B_VZ: return grid_to_host(b_.data(), out);
+    case PSV_RHO: return grid_to_host(rho_.data(), out);
+    case PSV_VP: return grid_to_host(vp_.data(), out);
+    case PSV_VS: return grid_to_host(vs_.data(), out);
+    case PSV_LAMBDA_KERNEL: return grid_to_host(k, out);
+    case PSV_MU_KERNEL: return grid_to_host(k + grid_elems_, out);
+    case PSV_DENSITY_L_KERNEL: return grid_to_host(k + 2 * grid_elems_, out);
+    case PSV_VP_KERNEL: return grid_to_host(vp_kernel_.data(), out);
+    case PSV_VS_KERNEL: return grid_to_host(vs_kernel_.data(), out);
+    case PSV_DENSITY_V_KERNEL: return grid_to_host(density_v_kernel_.data(), out);
+    case PSV_LA: {  // la = lm - 2*mu (src/fdModel.cpp:1046), not stored on the device
+      std::vector<double> mu(grid);
+      grid_to_host(lm_.data(), out);
+      grid_to_host(mu_.data(), mu.data());
+      for (size_t i = 0; i < grid; ++i) out[i] = out[i] - 2 * mu[i];
+      return;
+    }
+    case PSV_TAPER: {
+      for (int ix = 0; ix < c.nx; ++ix)
+        for (int iz = 0; iz < c.nz; ++iz) {
+          const int d = std::min(std::min(ix, c.nx - 1 - ix), std::min(iz, c.nz - 1 - iz)) + 1;
+          out[(size_t)ix * c.nz + iz] = taper_host_[std::min(d, c.np_boundary)];
+        }
+      return;
+    }
+    case PSV_T: std::memcpy(out, t_host_.data(), count * sizeof(double)); return;
+    case PSV_STF: std::memcpy(out, stf_host_.data(), count * sizeof(double)); return;
+    case PSV_MOMENT: std::memcpy(out, moment_host_.data(), count * sizeof(double)); return;
+    case PSV_RTF_UX:
+    case PSV_RTF_UZ:
+    case PSV_RTF_UX_TRUE:
+    case PSV_RTF_UZ_TRUE:
+    case PSV_A_STF_UX:
+    case PSV_A_STF_UZ: {
+      const DeviceBuffer *b[] = {&rtf_ux_, &rtf_uz_, &obs_ux_, &obs_uz_, &a_stf_ux_, &a_stf_uz_};
+      if (count) PSV_CUDA(cudaMemcpy(out, b[which - PSV_RTF_UX]->as<>(), count * sizeof(double), cudaMemcpyDeviceToHost));
+      return;
+    }
+    case PSV_ACCU_VX:
+    case PSV_ACCU_VZ:
+    case PSV_ACCU_TXX:
+    case PSV_ACCU_TZZ:
+    case PSV_ACCU_TXZ: {
+      const int field = which - PSV_ACCU_VX;
+      const size_t per_shot = (size_t)c.snapshots * grid;
+      for (int s = 0; s < c.n_shots; ++s) {
+        double *dst = out + (size_t)s * per_shot;
+        if (snapshots_[s].empty() || per_shot == 0) {
+          std::memset(dst, 0, per_shot * sizeof(double));
+        } else {
+          PSV_CUDA(cudaMemcpy2D(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
+                                c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost));
+        }
+      }
+      return;
+    }
+    default: throw invalid_argument("Unknown array id.");
+  }
+}
+
+void Model::set_array(psv_array which, const double *in, size_t count) {
+  bind();
+  if (count != array_size(which)) throw invalid_argument("Array size mismatch.");
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  double *k = lame_kernels_.as<double>();
+  switch (which) {
+    case PSV_VP: return grid_from_host(vp_.data(), in);
+    case PSV_VS: return grid_from_host(vs_.data(), in);
+    case PSV_RHO: return grid_from_host(rho_.data(), in);
+    case PSV_LAMBDA_KERNEL: return grid_from_host(k, in);
+    case PSV_MU_KERNEL: return grid_from_host(k + grid_elems_, in);
+    case PSV_DENSITY_L_KERNEL: return grid_from_host(k + 2 * grid_elems_, in);
+    case PSV_STF:
+      stf_host_.assign(in, in + count);
+      if (count) PSV_CUDA(cudaMemcpy(stf_.as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice));
+      return;
+    case PSV_MOMENT:
+      moment_host_.assign(in, in + count);
+      build_plans();
+      return;
+    case PSV_RTF_UX:
+    case PSV_RTF_UZ:
+    case PSV_RTF_UX_TRUE:
+    case PSV_RTF_UZ_TRUE:
+    case PSV_A_STF_UX:
+    case PSV_A_STF_UZ: {
+      DeviceBuffer *b[] = {&rtf_ux_, &rtf_uz_, &obs_ux_, &obs_uz_, &a_stf_ux_, &a_stf_uz_};
+      if (count) PSV_CUDA(cudaMemcpy(b[which - PSV_RTF_UX]->as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice));
+      return;
+    }
+    default: throw invalid_argument("This array cannot be set.");
+  }
+}
+
+void Model::set_parameter_fields(const double *vp, const double *vs, const double *rho, size_t count) {
+  if (count != (size_t)cfg_.nx * cfg_.nz)
+    throw invalid_argument("The input ndarray does not have the right shape.");
+  bind();
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  grid_from_host(vp_.data(), vp);
+  grid_from_host(vs_.data(), vs);
+  grid_from_host(rho_.data(), rho);
+  update_from_velocity();
+}
+
+// ---------------------------------------------------------------------------------------------
+// text I/O (same formats as the reference)
+// ---------------------------------------------------------------------------------------------
+void Model::write_receivers() {  // src/fdModel.cpp:971-1006
+  const Config &c = cfg_;
+  const size_t n = array_size(PSV_RTF_UX);
+  std::vector<double> ux(n), uz(n);
+  get_array(PSV_RTF_UX, ux.data(), n);
+  get_array(PSV_RTF_UZ, uz.data(), n);
+  for (int s = 0; s < c.n_shots; ++s) {
+    std::ofstream fx(c.observed_data_folder + "/rtf_ux" + std::to_string(s) + ".txt");
+    std::ofstream fz(c.observed_data_folder + "/rtf_uz" + std::to_string(s) + ".txt");
+    if (!fx.good() || !fz.good()) throw io_error("Cannot open receiver files for writing in '" + c.observed_data_folder + "'.");
+    fx.precision(std::numeric_limits<double>::digits10 + 10);
+    fz.precision(std::numeric_limits<double>::digits10 + 10);
+    for (int r = 0; r < c.nr; ++r) {
+      fx << std::endl;
+      fz << std::endl;
+      const size_t row = ((size_t)s * c.nr + r) * c.nt;
+      for (int it = 0; it < c.nt; ++it) {
+        fx << ux[row + it] << " ";
+        fz << uz[row + it] << " ";
+      }
+    }
+  }
+}
+
+void Model::load_receivers(bool verbose) {  // src/fdModel.cpp:1053-1126
+  const Config &c = cfg_;
+  const size_t n = array_size(PSV_RTF_UX_TRUE);
+  std::vector<double> ux(n), uz(n);
+  for (int s = 0; s < c.n_shots; ++s) {
+    std::ifstream fx(c.observed_data_folder + "/rtf_ux" + std::to_string(s) + ".txt");
+    std::ifstream fz(c.observed_data_folder + "/rtf_uz" + std::to_string(s) + ".txt");
+    if (verbose) {
+      std::cout << "File for ux data at shot " << s << " is "
+                << (fx.good() ? "good (exists at least)." : "ungood.") << std::endl;
+      std::cout << "File for uz data at shot " << s << " is "
+                << (fz.good() ? "good (exists at least)." : "ungood.") << std::endl;
+    }
+    if (!fx.good() || !fz.good()) throw invalid_argument("Not all data is present!");
+    for (int r = 0; r < c.nr; ++r)
+      for (int it = 0; it < c.nt; ++it) {
+        const size_t q = ((size_t)s * c.nr + r) * c.nt + it;
+        fx >> ux[q];
+        fz >> uz[q];
+      }
+    if (!fx.good() || !fz.good()) {
+      std::cout << "Received bad state of file at end of reading! Does the data match the set up?" << std::endl;
+      throw invalid_argument("Not enough data is present!");
+    }
+    double extra;
+    fx >> extra;
+    fz >> extra;
+    if (fx.good() || fz.good()) {
+      std::cout << "Received good state of file past reading! Does the data match the set up?" << std::endl;
+      throw invalid_argument("Too much data is present!");
+    }
+  }
+  set_array(PSV_RTF_UX_TRUE, ux.data(), n);
+  set_array(PSV_RTF_UZ_TRUE, uz.data(), n);
+}
+
+void Model::write_sources() {  // src/fdModel.cpp:1008-1032
+  const Config &c = cfg_;
+  for (int s = 0; s < c.n_shots; ++s) {
+    std::ofstream f(c.stf_folder + "/sources_shot_" + std::to_string(s) + ".txt");
+    if (!f.good()) throw io_error("Cannot open source file for writing in '" + c.stf_folder + "'.");
+    f.precision(std::numeric_limits<double>::digits10 + 10);
+    for (int src : c.which_source_to_fire_in_which_shot[s]) {
+      f << std::endl;
+      for (int it = 0; it < c.nt; ++it) f << stf_host_[(size_t)src * c.nt + it] << " ";
+    }
+  }
+}
+
+void Model::write_kernels() {  // src/fdModel.cpp:1326-1356
+  const Config &c = cfg_;
+  const size_t n = (size_t)c.nx * c.nz;
+  const psv_array ids[] = {PSV_VP_KERNEL, PSV_VS_KERNEL, PSV_DENSITY_V_KERNEL};
+  const char *names[] = {"kernel_vp.txt", "kernel_vs.txt", "kernel_density.txt"};
+  std::vector<double> k(n);
+  for (int j = 0; j < 3; ++j) {
+    get_array(ids[j], k.data(), n);
+    std::ofstream f(names[j]);
+    if (!f.good()) throw io_error(std::string("Cannot open ") + names[j] + " for writing.");
+    for (int ix = 0; ix < c.nx; ++ix) {
+      for (int iz = 0; iz < c.nz; ++iz) f << k[(size_t)ix * c.nz + iz] << " ";
+      f << std::endl;
+    }
+  }
+}
+
+void Model::write_wavefield_files(int it) {  // src/fdModel.cpp:753-776
+  const Config &c = cfg_;
+  const size_t n = (size_t)c.nx * c.nz;
+  std::vector<double> a(n), b(n);
+  get_array(PSV_VX, a.data(), n);
+  get_array(PSV_VZ, b.data(), n);
+  std::ofstream fx("snapshots/vx" + zero_pad(it, 5) + ".txt"), fz("snapshots/vz" + zero_pad(it, 5) + ".txt");
+  for (int ix = 0; ix < c.nx; ++ix) {
+    for (int iz = 0; iz < c.nz; ++iz) {
+      fx << a[(size_t)ix * c.nz + iz] << " ";
+      fz << b[(size_t)ix * c.nz + iz] << " ";
+    }
+    fx << std::endl;
+    fz << std::endl;
+  }
+}
+
+void Model::load_model(const std::string &de_path, const std::string &vp_path, const std::string &vs_path,
+                       bool verbose) {  // src/fdModel.cpp:1185-1289
+  const Config &c = cfg_;
+  std::ifstream de(de_path), vp(vp_path), vs(vs_path);
+  if (verbose) {
+    std::cout << "Loading models." << std::endl;
+    std::cout << "File: " << de_path << std::endl;
+    std::cout << "File for density is " << (de.good() ? "good (exists at least)." : "ungood.") << std::endl;
+    std::cout << "File: " << vp_path << std::endl;
+    std::cout << "File for P-wave velocity is " << (vp.good() ? "good (exists at least)." : "ungood.") << std::endl;
+    std::cout << "File: " << vs_path << std::endl;
+    std::cout << "File for S-wave velocity is " << (vs.good() ? "good (exists at least)." : "ungood.") << std::endl;
+  }
+  if (!de.good() || !vp.good() || !vs.good())
+    throw invalid_argument("The files for target models don't seem to exist.\r\nPaths:\r\n\tDensity target: " +
+                           de_path + "\r\n\tP-wave target : " + vp_path + "\r\n\tS-wave target : " + vs_path + "\r\n");
+  const size_t n = (size_t)c.nx * c.nz;
+  std::vector<double> r(n), p(n), s(n);
+  for (size_t i = 0; i < n; ++i) {  // ix-major, iz fastest; (the reference also prints one line per point)
+    de >> r[i];
+    vp >> p[i];
+    vs >> s[i];
+    if (!de.good() || !vp.good() || !vs.good())
+      throw invalid_argument("Received bad state of one of the files at end of reading. Does the data match the domain?");
+  }
+  double extra;
+  de >> extra;
+  vp >> extra;
+  vs >> extra;
+  if (de.good() || vp.good() || vs.good()) {
+    std::cout << "Received good state of file past reading. Does the data match the domain?" << std::endl;
+    throw invalid_argument("Too much data is present!");
+  }
+  set_parameter_fields(p.data(), s.data(), r.data(), n);
+  if (verbose) std::cout << std::endl;
+}
+
+void Model::load_vector(const std::string &path, bool verbose, double *out, size_t n) {  // :1517-1572
+  const Config &c = cfg_;
+  if (n != (size_t)3 * c.nx_free * c.nz_free) throw invalid_argument("load_vector: output has the wrong length.");
+  std::ifstream f(path);
+  if (verbose) {
+    std::cout << "Loading model vector." << std::endl;
+    std::cout << "File: " << path << std::endl;
+    std::cout << "File is " << (f.good() ? "good (exists at least)." : "ungood.") << std::endl;
+  }
+  if (!f.good())
+    throw invalid_argument("The files for target models don't seem to exist.\r\nPaths:\r\n\tDensity target: " + path + "\r\n");
+  for (size_t i = 0; i < n; ++i) f >> out[i];
+  if (!f.good()) {
+    std::cout << "Received bad state of one of the files at end of reading. Does the data match the domain?" << std::endl;
+    throw invalid_argument("Not enough data is present!");
+  }
+  double extra;
+  f >> extra;
+  if (f.good()) {
+    std::cout << "Received good state of file past reading. Does the data match the domain?" << std::endl;
+    throw invalid_argument("Too much data is present!");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// options / statistics
+// ---------------------------------------------------------------------------------------------
+void Model::set_option(const std::string &name, long long v) {
+  if (name == "variant") {
+    if (v < 0 || v > 1) throw invalid_argument("variant must be 0 or 1");
+    variant_ = (int)v;
+  } else if (name == "exact") {
+    exact_ = v != 0;
+  } else if (name == "profile") {
+    profile_ = v != 0;
+  } else if (name == "strip") {
+    if (v < 1) throw invalid_argument("strip must be >= 1");
+    strip_ = (int)v;
+  } else if (name == "block") {
+    if (v != 32 && v != 64 && v != 96 && v != 128) throw invalid_argument("block must be 32, 64, 96 or 128");
+    block_ = (int)v;
+  } else {
+    throw invalid_argument("Unknown option '" + name + "'.");
+  }
+}
+
+long long Model::get_option(const std::string &name) const {
+  if (name == "variant") return variant_;
+  if (name == "exact") return exact_;
+  if (name == "profile") return profile_;
+  if (name == "strip") return strip_;
+  if (name == "block") return block_;
+  throw invalid_argument("Unknown option '" + name + "'.");
+}
+
+double Model::get_stat(const std::string &name) const {
+  if (name == "elapsed_ms") return stat_elapsed_ms_;
+  if (name == "launches") return (double)stat_launches_;
+  if (name == "stress_ms") return stat_stress_ms_;
+  if (name == "velocity_ms") return stat_velocity_ms_;
+  if (name == "pitch") return ld_;
+  if (name == "snapshot_bytes_per_shot") return 5.0 * n_snap_alloc_ * (double)grid_elems_ * sizeof(double);
+  throw invalid_argument("Unknown statistic '" + name + "'.");
+}
+
+}  // namespace psv

@@ -1,0 +1,178 @@
+// psv::Model -- one fdModel object living on one CUDA device.
+// Replaces the state + methods of the reference class fdModel (src/fdModel.h:35-318).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/psvwave_b200.h"
+#include "config.hpp"
+
+namespace psv {
+
+struct cuda_error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+struct state_error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+struct io_error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+void cuda_check(cudaError_t e, const char *what, const char *file, int line);
+#define PSV_CUDA(expr) ::psv::cuda_check((expr), #expr, __FILE__, __LINE__)
+
+// Owning device allocation (zero-initialised).
+class DeviceBuffer {
+ public:
+  DeviceBuffer() = default;
+  explicit DeviceBuffer(size_t bytes) { allocate(bytes); }
+  ~DeviceBuffer() { release(); }
+  DeviceBuffer(const DeviceBuffer &) = delete;
+  DeviceBuffer &operator=(const DeviceBuffer &) = delete;
+  DeviceBuffer(DeviceBuffer &&o) noexcept : p_(o.p_), bytes_(o.bytes_) { o.p_ = nullptr; o.bytes_ = 0; }
+  DeviceBuffer &operator=(DeviceBuffer &&o) noexcept {
+    if (this != &o) {
+      release();
+      p_ = o.p_;
+      bytes_ = o.bytes_;
+      o.p_ = nullptr;
+      o.bytes_ = 0;
+    }
+    return *this;
+  }
+  void allocate(size_t bytes);
+  void release();
+  template <class T = double>
+  T *as() const { return static_cast<T *>(p_); }
+  size_t bytes() const { return bytes_; }
+  bool empty() const { return p_ == nullptr; }
+
+ private:
+  void *p_ = nullptr;
+  size_t bytes_ = 0;
+};
+
+// A pitched (nx, ld) grid array with its guard bands; data() points at element (0, 0).
+struct GridArray {
+  DeviceBuffer buf;
+  double *data() const { return buf.as<double>() + guard; }
+  size_t guard = 0;
+};
+
+class Model {
+ public:
+  explicit Model(Config cfg, int device);
+  Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
+  ~Model();
+
+  const Config &config() const { return cfg_; }
+  int device() const { return device_; }
+
+  // hot path
+  void forward_simulate(int i_shot, bool store_fields, bool verbose, bool output_wavefields);
+  void adjoint_simulate(int i_shot, bool verbose);
+  double calculate_l2_misfit();
+  double calculate_l2_misfit_shot(int i_shot);
+  void calculate_l2_adjoint_sources();
+  void reset_kernels();
+  void map_kernels_to_velocity();
+  void update_from_velocity();
+  void run_model(bool verbose, bool simulate_adjoint);
+
+  void get_model_vector(double *out, size_t n);
+  void set_model_vector(const double *in, size_t n);
+  void get_gradient_vector(double *out, size_t n);
+
+  size_t array_size(psv_array which) const;
+  void get_array(psv_array which, double *out, size_t count);
+  void set_array(psv_array which, const double *in, size_t count);
+  void set_parameter_fields(const double *vp, const double *vs, const double *rho, size_t count);
+
+  // text I/O
+  void write_receivers();
+  void load_receivers(bool verbose);
+  void write_sources();
+  void write_kernels();
+  void load_model(const std::string &de, const std::string &vp, const std::string &vs, bool verbose);
+  void load_vector(const std::string &path, bool verbose, double *out, size_t n);
+
+  void release_snapshots(int i_shot);
+  void kernel_buffer(void **ptr, size_t *count) const;
+  void synchronize();
+
+  void set_option(const std::string &name, long long value);
+  long long get_option(const std::string &name) const;
+  double get_stat(const std::string &name) const;
+
+  double misfit() const { return misfit_; }
+
+ private:
+  struct ShotPlan {  // per-shot device lists for the point operations
+    DeviceBuffer ops, heads;
+    int n_heads = 0;
+  };
+
+  void allocate();
+  void initialize_host_tables();
+  void build_plans();
+  void bind() const;  // cudaSetDevice
+  GridArray make_grid() const;
+  void grid_to_host(const double *dev, double *host) const;
+  void grid_from_host(double *dev, const double *host) const;
+  void zero_dynamic_fields();
+  void ensure_snapshots(int i_shot);
+  double *snapshot_ptr(int i_shot, int field, int snap) const;
+  void check_shot(int i_shot) const;
+  double misfit_of_range(size_t first, size_t count);
+  void launch_stress(double sdt, int mode, int i_shot, int snap);
+  void launch_velocity(double sdt);
+  void write_wavefield_files(int it);
+
+  Config cfg_;
+  int device_ = 0;
+  cudaStream_t stream_ = nullptr;
+  cudaEvent_t ev_begin_ = nullptr, ev_end_ = nullptr;
+  std::vector<cudaEvent_t> prof_events_;
+
+  // geometry of the device layout
+  int ld_ = 0;            // row pitch in doubles
+  size_t grid_elems_ = 0; // nx * ld
+  size_t guard_ = 0;
+  int n_snap_alloc_ = 0;  // ceil(nt / snapshot_interval)
+
+  // grid arrays
+  GridArray vx_, vz_, txx_, tzz_, txz_;       // dynamic fields
+  GridArray vp_, vs_, rho_, lm_, mu_, b_;     // medium
+  DeviceBuffer lame_kernels_;                 // [lambda | mu | density_l], each nx*ld
+  GridArray vp_kernel_, vs_kernel_, density_v_kernel_;
+  DeviceBuffer taper_table_;                  // np_boundary + 1 values
+  std::vector<double> taper_host_;            // the same table on the host
+
+  // signals
+  std::vector<double> t_host_, stf_host_, moment_host_;
+  DeviceBuffer stf_;                                      // [n_sources][nt]
+  DeviceBuffer rtf_ux_, rtf_uz_, obs_ux_, obs_uz_, a_stf_ux_, a_stf_uz_;  // [n_shots][nr][nt]
+  DeviceBuffer rec_index_, rec_next_, rec_heads_;
+  int n_rec_heads_ = 0;
+  std::vector<ShotPlan> plans_;
+  std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
+  DeviceBuffer scratch_;                 // reduction partials / vectors
+
+  double misfit_ = 0.0;
+
+  // options / statistics
+  int variant_ = 1;
+  bool exact_ = false;
+  bool profile_ = false;
+  int strip_ = 16, block_ = 128;
+  double stat_elapsed_ms_ = 0, stat_stress_ms_ = 0, stat_velocity_ms_ = 0;
+  long long stat_launches_ = 0;
+};
+
+}  // namespace psv

@@ -1,0 +1,122 @@
+// Point-wise arithmetic of the P-SV velocity-stress scheme, shared by every kernel variant.
+//
+// Two arithmetic policies:
+//   ExactMath  every operation is an explicitly rounded IEEE-754 double operation
+//              (__dmul_rn/__dadd_rn/__ddiv_rn are never contracted into FMAs) issued in the
+//              reference's literal evaluation order (src/fdModel.cpp:615-642, 661-676,
+//              832-858), so the result is BIT-IDENTICAL to the reference's x86-64 build.
+//   FastMath   the same formulas with divisions by dx/dz folded into precomputed
+//              reciprocals and FMA contraction allowed; differs from the reference at the
+//              1e-15 relative level (budget: 1e-10), and keeps the kernels HBM-bound.
+#pragma once
+
+#include <cuda_runtime.h>
+
+namespace psv {
+
+struct ExactMath {
+  static constexpr bool kExact = true;
+  __device__ __forceinline__ static double mul(double a, double b) { return __dmul_rn(a, b); }
+  __device__ __forceinline__ static double add(double a, double b) { return __dadd_rn(a, b); }
+  __device__ __forceinline__ static double sub(double a, double b) { return __dsub_rn(a, b); }
+  __device__ __forceinline__ static double div(double a, double b) { return __ddiv_rn(a, b); }
+};
+
+struct FastMath {
+  static constexpr bool kExact = false;
+  __device__ __forceinline__ static double mul(double a, double b) { return a * b; }
+  __device__ __forceinline__ static double add(double a, double b) { return a + b; }
+  __device__ __forceinline__ static double sub(double a, double b) { return a - b; }
+  __device__ __forceinline__ static double div(double a, double b) { return a / b; }
+};
+
+// Scalars of one sweep.  sdt = +dt (forward) or -dt (adjoint): f - dt*X == f + (-dt)*X
+// bit for bit, so one body serves both time directions (src/fdModel.cpp:882-946).
+struct SweepConsts {
+  double sdt;       // signed time step
+  double dx, dz;    // grid spacing (ExactMath divides by these)
+  double rdx, rdz;  // reciprocals (FastMath)
+  double c1, c2;    // 9/8, 1/24 (src/fdModel.h:201-202)
+};
+
+// Staggered 4th-order difference: c1*(a - b) + c2*(c - d).
+template <class M>
+__device__ __forceinline__ double diff4(const SweepConsts &k, double a, double b, double c, double d) {
+  return M::add(M::mul(k.c1, M::sub(a, b)), M::mul(k.c2, M::sub(c, d)));
+}
+
+// Cerjan taper value of grid point (ix, iz): table[min(np, 1 + distance to nearest edge)]
+// (src/fdModel.cpp:263-298 builds exactly this as a full array; the table holds the np+1
+// distinct values, computed on the host with the reference's expression).
+__device__ __forceinline__ double taper_at(const double *__restrict__ table, int np, int ix, int iz,
+                                           int nx, int nz) {
+  int d = min(min(ix, nx - 1 - ix), min(iz, nz - 1 - iz)) + 1;
+  d = min(d, np);
+  return __ldg(table + d);
+}
+
+// Stress update of one point (src/fdModel.cpp:615-642).  la = lm - 2*mu is recomputed with
+// the operation update_from_velocity uses (src/fdModel.cpp:1046), so it equals the
+// reference's stored `la` bit for bit and the array need not be read.
+//   dxp_vx = D+x vx, dzm_vz = D-z vz, dzp_vx = D+z vx, dxm_vz = D-x vz
+template <class M>
+__device__ __forceinline__ void stress_update(const SweepConsts &k, double dxp_vx, double dzm_vz,
+                                              double dzp_vx, double dxm_vz, double lm, double mu,
+                                              double tp, double &txx, double &tzz, double &txz) {
+  const double la = M::sub(lm, M::mul(2.0, mu));
+  if (M::kExact) {
+    txx = M::mul(tp, M::add(txx, M::mul(k.sdt, M::add(M::div(M::mul(lm, dxp_vx), k.dx),
+                                                       M::div(M::mul(la, dzm_vz), k.dz)))));
+    tzz = M::mul(tp, M::add(tzz, M::mul(k.sdt, M::add(M::div(M::mul(la, dxp_vx), k.dx),
+                                                       M::div(M::mul(lm, dzm_vz), k.dz)))));
+    txz = M::mul(tp, M::add(txz, M::mul(M::mul(k.sdt, mu),
+                                        M::add(M::div(dzp_vx, k.dz), M::div(dxm_vz, k.dx)))));
+  } else {
+    const double ex = dxp_vx * k.rdx, ez = dzm_vz * k.rdz;
+    txx = tp * (txx + k.sdt * (lm * ex + la * ez));
+    tzz = tp * (tzz + k.sdt * (la * ex + lm * ez));
+    txz = tp * (txz + (k.sdt * mu) * (dzp_vx * k.rdz + dxm_vz * k.rdx));
+  }
+}
+
+// Velocity update of one point (src/fdModel.cpp:661-676); b = 1/rho (b_vx == b_vz).
+//   dxm_txx = D-x txx, dzm_txz = D-z txz, dxp_txz = D+x txz, dzp_tzz = D+z tzz
+template <class M>
+__device__ __forceinline__ void velocity_update(const SweepConsts &k, double dxm_txx, double dzm_txz,
+                                                double dxp_txz, double dzp_tzz, double b, double tp,
+                                                double &vx, double &vz) {
+  if (M::kExact) {
+    const double bs = M::mul(b, k.sdt);
+    vx = M::mul(tp, M::add(vx, M::mul(bs, M::add(M::div(dxm_txx, k.dx), M::div(dzm_txz, k.dz)))));
+    vz = M::mul(tp, M::add(vz, M::mul(bs, M::add(M::div(dxp_txz, k.dx), M::div(dzp_tzz, k.dz)))));
+  } else {
+    const double bs = b * k.sdt;
+    vx = tp * (vx + bs * (dxm_txx * k.rdx + dzm_txz * k.rdz));
+    vz = tp * (vz + bs * (dxp_txz * k.rdx + dzp_tzz * k.rdz));
+  }
+}
+
+// Sensitivity-kernel accumulation of one point (src/fdModel.cpp:832-858): forward snapshot
+// (f*) against the adjoint state *before* this step's update.  sidt = snapshot_interval*dt.
+template <class M>
+__device__ __forceinline__ void kernel_accumulate(double sidt, double lm, double mu, double fvx,
+                                                  double fvz, double fxx, double fzz, double fxz,
+                                                  double vx, double vz, double txx, double tzz,
+                                                  double txz, double &k_rho, double &k_lam,
+                                                  double &k_mu) {
+  const double la = M::sub(lm, M::mul(2.0, mu));
+  k_rho = M::sub(k_rho, M::mul(sidt, M::add(M::mul(fvx, vx), M::mul(fvz, vz))));
+  // q(a, b) = a - (b*la)/lm
+  const double F1 = M::sub(fxx, M::div(M::mul(fzz, la), lm));
+  const double F2 = M::sub(fzz, M::div(M::mul(fxx, la), lm));
+  const double A1 = M::sub(txx, M::div(M::mul(tzz, la), lm));
+  const double A2 = M::sub(tzz, M::div(M::mul(txx, la), lm));
+  const double d0 = M::sub(lm, M::div(M::mul(la, la), lm));
+  const double den = M::mul(d0, d0);
+  k_lam = M::add(k_lam, M::div(M::mul(sidt, M::mul(M::add(F1, F2), M::add(A1, A2))), den));
+  const double t1 = M::div(M::add(M::mul(A1, F1), M::mul(A2, F2)), den);
+  const double t2 = M::mul(2.0, M::div(M::mul(txz, fxz), M::mul(M::mul(4.0, mu), mu)));
+  k_mu = M::add(k_mu, M::mul(M::mul(sidt, 2.0), M::add(t1, t2)));
+}
+
+}  // namespace psv
