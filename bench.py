@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""Benchmark of the P-SV time loop (BASELINE.json metric: grid-point updates/s, fwd+adj, and
+FWI gradient time per shot; % of the HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (config.workload = "C2-marmousi-scale-gradient"): synthetic
+Marmousi-scale elastic model, 3000 x 1220 inner grid + 50-point Cerjan frame = 3100 x 1320
+points, nt = 4000, snapshot every 20 steps, 300 receivers, shots of 2 stacked sources.
+One STEP = the FWI gradient contribution of ONE shot per GPU:
+    forward_simulate(shot, store_fields=True)  -> per-shot L2 misfit -> adjoint sources
+    -> adjoint_simulate(shot) with in-loop accumulation of the rho/lambda/mu kernels
+    (N > 1: + one all-reduce of the three Lame kernels over NCCL, every step)
+i.e. 2 * nx * nz * nt grid-point updates per GPU per step.  Shots are dealt round-robin to
+the ranks (weak scaling: one shot per GPU per step).
+
+`value` is timed with CUDA events on the solver's stream with all inputs resident in HBM.
+`e2e` is the same step through the public Python API with HOST buffers: set_parameter_fields
+from pinned host memory before, get_gradient_vector to the host after, inside the timed region.
+`roofline` is the dominant sweep kernel: algorithmic bytes per launch over its
+mean CUDA-event duration sampled inside the timed steps.
+`cpu_baseline` / `--impl reference`: the UNMODIFIED reference core (oracle/_ref, OpenMP, all
+host threads) on a bounded sample of the same workload (same grid and medium, fewer time
+steps).  Nothing here reads /root/reference at run time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = "C2-marmousi-scale-gradient"
+GEOM = dict(nx_inner=3000, nz_inner=1220, np_boundary=50, nt=4000, snapshot_interval=20, n_shots=16, nr=300)
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic Marmousi-scale configuration + medium
+# ---------------------------------------------------------------------------------------------
+def workload_config(nt: int, n_shots: int, geom=GEOM) -> dict:
+    nxi, nzi = geom["nx_inner"], geom["nz_inner"]
+    n_sources = 2 * n_shots
+    xs = np.linspace(150, nxi - 150, n_sources).round().astype(int)
+    return dict(
+        nt=nt, nx_inner=nxi, nz_inner=nzi, nx_inner_boundary=10, nz_inner_boundary=10, dx=2.5, dz=2.5, dt=2.5e-4,
+        np_boundary=geom["np_boundary"], np_factor=0.0075, scalar_rho=2200.0, scalar_vp=3000.0, scalar_vs=1600.0,
+        npx=1, npz=1, peak_frequency=8.0, source_timeshift=0.0, delay_cycles_per_shot=8.0,
+        n_sources=n_sources, n_shots=n_shots, ix_sources=[int(v) for v in xs], iz_sources=[8] * n_sources,
+        moment_angles=[float(a) for a in np.linspace(0, 170, n_sources)],
+        which_source_to_fire_in_which_shot=[[2 * s, 2 * s + 1] for s in range(n_shots)],
+        nr=geom["nr"], ix_receivers=[int(v) for v in np.linspace(20, nxi - 20, geom["nr"]).round()],
+        iz_receivers=[10] * geom["nr"], snapshot_interval=geom["snapshot_interval"],
+        observed_data_folder=".", stf_folder=".")
+
+
+def write_ini(path: str, cfg: dict) -> None:
+    def lst(x):
+        if isinstance(x, (list, tuple)):
+            return "{" + ", ".join(lst(v) for v in x) + "}"
+        return repr(x)
+    sections = {
+        "domain": ["nt", "nx_inner", "nz_inner", "nx_inner_boundary", "nz_inner_boundary", "dx", "dz", "dt"],
+        "boundary": ["np_boundary", "np_factor"],
+        "medium": ["scalar_rho", "scalar_vp", "scalar_vs"],
+        "sources": ["peak_frequency", "n_sources", "n_shots", "source_timeshift", "delay_cycles_per_shot",
+                    "moment_angles", "ix_sources", "iz_sources", "which_source_to_fire_in_which_shot"],
+        "receivers": ["nr", "ix_receivers", "iz_receivers"],
+        "inversion": ["snapshot_interval"],
+        "basis": ["npx", "npz"],
+        "output": ["observed_data_folder", "stf_folder"],
+    }
+    with open(path, "w") as fh:
+        for sec, keys in sections.items():
+            fh.write(f"[{sec}]\n")
+            for k in keys:
+                v = cfg[k]
+                fh.write(f"{k} = {v if isinstance(v, str) else lst(v)}\n")
+
+
+def marmousi_like(nx: int, nz: int, seed: int = 1234, blob_seed: int | None = None):
+    """40 dipping layers, vp 1500..4700 m/s increasing with depth + 5 % smoothed noise,
+    vs = vp/1.9 floored at 400 m/s, rho = 310 vp^0.25 (Gardner).  blob_seed adds a +5 %
+    Gaussian-blob perturbation (the 'true' model the observed data come from)."""
+    rng = np.random.default_rng(seed)
+    x = np.arange(nx)[:, None] / nx
+    z = np.arange(nz)[None, :] / nz
+    dip = 0.15 * x + 0.03 * np.sin(6.0 * x + 1.0)
+    layer = np.clip(np.floor((z + dip) / 1.2 * 40), 0, 39).astype(int)
+    steps = np.sort(rng.uniform(0, 1, 40)) * 0.6 + np.linspace(0, 0.4, 40)
+    vp = 1500.0 + 3200.0 * steps[layer]
+    noise = rng.standard_normal((nx // 8 + 2, nz // 8 + 2))
+    noise = np.kron(noise, np.ones((8, 8)))[:nx, :nz]
+    for _ in range(2):  # cheap smoothing
+        noise = (noise + np.roll(noise, 1, 0) + np.roll(noise, -1, 0) + np.roll(noise, 1, 1) + np.roll(noise, -1, 1)) / 5
+    vp = np.clip(vp * (1 + 0.05 * noise / max(noise.std(), 1e-12) * 0.5), 1500.0, 4900.0)
+    if blob_seed is not None:
+        r2 = np.random.default_rng(blob_seed)
+        for _ in range(6):
+            cx, cz, w = r2.uniform(0.1, 0.9), r2.uniform(0.2, 0.9), r2.uniform(0.03, 0.08)
+            vp = vp * (1 + 0.05 * np.exp(-((x - cx) ** 2 + (z - cz) ** 2) / (2 * w * w)))
+    vs = np.maximum(vp / 1.9, 400.0)
+    rho = 310.0 * vp ** 0.25
+    return np.ascontiguousarray(vp), np.ascontiguousarray(vs), np.ascontiguousarray(rho)
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                if out.returncode == 0 and out.stdout.strip():
+                    self.rows.append([c.strip() for c in out.stdout.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self) -> dict:
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(sm), "power_w_max": max(float(r[6]) for r in self.rows)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference arm / cpu baseline: unmodified reference core on a bounded sample
+# ---------------------------------------------------------------------------------------------
+def omp_threads() -> int:
+    import ctypes
+    try:
+        return int(ctypes.CDLL("libgomp.so.1").omp_get_max_threads())
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_sample_run(target_seconds: float, geom=GEOM, steps: int = 1, warmup: int = 0):
+    """Time forward(store)+adjoint of shot 0 on the CPU checker for `nt_sample` time steps of
+    the same grid/medium.  Returns (updates per second, seconds per step, description, kind)."""
+    from oracle import oracle
+    kind = "reference" if oracle.ref_available() else "port"
+    si = geom["snapshot_interval"]
+
+    def make(nt):
+        cfg = workload_config(nt, 1, geom)
+        d = tempfile.mkdtemp(prefix="psv_cpu_")
+        ini = os.path.join(d, "sample.ini")
+        write_ini(ini, cfg)
+        m = oracle.RefModel(ini) if kind == "reference" else oracle.OracleModel(ini)
+        m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
+        return m
+
+    def gradient(m):
+        t0 = time.perf_counter()
+        m.forward_simulate(0, True)
+        m.calculate_l2_misfit()
+        m.calculate_l2_adjoint_sources()
+        m.reset_kernels()
+        m.adjoint_simulate(0)
+        m.map_kernels_to_velocity()
+        return time.perf_counter() - t0
+
+    m = make(si)  # calibration: one snapshot interval
+    gradient(m)
+    t_cal = gradient(m)
+    per_step = t_cal / si
+    nt = int(max(si, min(geom["nt"], 1000, round(target_seconds / per_step / si) * si)))
+    if nt != si:
+        del m
+        m = make(nt)
+    for _ in range(warmup):
+        gradient(m)
+    times = [gradient(m) for _ in range(max(1, steps))]
+    updates = 2.0 * m.nx * m.nz * nt
+    best = min(times)
+    sample = (f"{kind} core (OpenMP, -O3), shot 0 of {WORKLOAD}: same {m.nx}x{m.nz} grid and medium, "
+              f"nt={nt} of {geom['nt']} time steps, forward(store)+adjoint, best of {len(times)}")
+    return updates / best, sum(times) / len(times), sample, kind, nt
+
+
+def run_reference_arm(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = omp_threads()
+    rate, sec, sample, kind, nt = cpu_sample_run(12.0, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": "grid-point updates/s (fwd+adj)", "value": rate, "unit": "updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "grid": [GEOM["nx_inner"] + 2 * GEOM["np_boundary"],
+                                                  GEOM["nz_inner"] + 2 * GEOM["np_boundary"]],
+                   "nt_sample": nt, "nt": GEOM["nt"], "snapshot_interval": GEOM["snapshot_interval"]},
+        "cpu_baseline": {"value": rate, "unit": "updates/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": rate, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    emit(line)
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def pinned_copy(a: np.ndarray):
+    import torch
+    t = torch.empty(a.shape, dtype=torch.float64, pin_memory=True)
+    t.numpy()[...] = a
+    return t  # keep the tensor alive; use .numpy() views
+
+
+def run_ours(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    import psvwave_b200
+    from psvwave_b200.parallel import ShotParallel
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if psvwave_b200.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    psvwave_b200.set_default_device(local)
+
+    geom = dict(GEOM)
+    if args.nt:
+        geom["nt"] = args.nt
+    n_shots = max(geom["n_shots"], world)
+    cfg = workload_config(geom["nt"], n_shots, geom)
+    tmp = tempfile.mkdtemp(prefix=f"psv_bench_{rank}_")
+    ini = os.path.join(tmp, "c2.ini")
+    write_ini(ini, cfg)
+    m = psvwave_b200.fdModel(ini)
+    for kv in args.option:
+        k, v = kv.split("=")
+        m._set_option(k, int(v))
+    nx, nz, nt = m.nx, m.nz, m.nt
+    start = marmousi_like(nx, nz)
+    true = marmousi_like(nx, nz, blob_seed=4321)
+    sp = ShotParallel(m, rank=rank, world_size=world)
+    shots = sp.my_shots()
+    need = args.steps + args.warmup
+    my = [shots[i % len(shots)] for i in range(need)]
+
+    # observed data = synthetics of the perturbed model for the shots this rank will touch
+    m.set_parameter_fields(*true)
+    for s in sorted(set(my)):
+        m.forward_simulate(s, False)
+    m.set_observed_data(*m.get_synthetic_data())
+    m.set_parameter_fields(*start)
+    pinned = [pinned_copy(a) for a in start]
+    host_model = [t.numpy() for t in pinned]
+
+    def step(shot, e2e):
+        if e2e:
+            m.set_parameter_fields(*host_model)
+        m.reset_kernels()
+        m.forward_simulate(shot, True)
+        launches = m._get_stat("launches")
+        prof = [m._get_stat("stress_ms"), m._get_stat("velocity_ms")]
+        mis = m.calculate_l2_misfit_shot(shot)
+        m.calculate_l2_adjoint_sources()
+        m.adjoint_simulate(shot)
+        launches += m._get_stat("launches") + 3
+        prof += [m._get_stat("stress_ms"), m._get_stat("velocity_ms")]
+        m.release_snapshots(shot)
+        sp.allreduce_kernels()
+        m.map_kernels_to_velocity()
+        g = m.get_gradient_vector() if e2e else None
+        return mis, launches + 1, prof, g
+
+    def barrier():
+        m.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    m._set_option("profile", 1)
+    for i in range(args.warmup):
+        step(my[i], False)
+    barrier()
+    launches_total, profs = 0, []
+    with ClockSampler(local) as clocks:
+        t_wall = time.perf_counter()
+        m._timer_start()
+        for i in range(args.steps):
+            _, l, p, _ = step(my[args.warmup + i], False)
+            launches_total += l
+            profs.append(p)
+        dev_ms = m._timer_stop()
+        barrier()
+        wall_ms = (time.perf_counter() - t_wall) * 1e3
+    m._set_option("profile", 0)
+
+    # end to end through the public API with host buffers
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        _, _, _, g = step(my[args.warmup + i], True)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    grad_bytes = int(g.nbytes)
+
+    def rank_max(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    dev_ms, wall_ms, e2e_ms = rank_max(dev_ms), rank_max(wall_ms), rank_max(e2e_ms)
+    updates_per_step = 2.0 * nx * nz * nt * world
+    value = updates_per_step * args.steps / (dev_ms * 1e-3)
+    e2e_value = updates_per_step * args.steps / (e2e_ms * 1e-3)
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        P = np.array(profs)  # columns: fwd stress, fwd velocity, adj stress, adj velocity (ms / launch)
+        pts = float(nx) * nz
+        bytes_per_launch = {"stress": 12 * 8 * pts, "velocity": 10 * 8 * pts, "fused": 16 * 8 * pts}
+        fused = m._get_option("variant") >= 2
+        if fused:
+            ms = float(P[:, [0, 2]].mean())
+            kern, nbytes = "fused stress+velocity sweep", bytes_per_launch["fused"]
+        else:
+            s_ms, v_ms = float(P[:, [0, 2]].mean()), float(P[:, [1, 3]].mean())
+            if s_ms >= v_ms:
+                kern, ms, nbytes = "stress sweep", s_ms, bytes_per_launch["stress"]
+            else:
+                kern, ms, nbytes = "velocity sweep", v_ms, bytes_per_launch["velocity"]
+        achieved = nbytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(kern)
+        roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": nbytes, "ms_per_launch": ms,
+                    "all_ms_per_launch": {"fwd_stress": float(P[:, 0].mean()), "fwd_velocity": float(P[:, 1].mean()),
+                                          "adj_stress": float(P[:, 2].mean()), "adj_velocity": float(P[:, 3].mean())}}
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            rate, _, sample, kind, _ = cpu_sample_run(15.0)
+            cpu = {"value": rate, "unit": "updates/s", "cores": omp_threads(), "kind": kind, "sample": sample}
+        line = {
+            "metric": "grid-point updates/s (fwd+adj)", "value": value, "unit": "updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "grid": [nx, nz], "nt": nt, "snapshot_interval": m.snapshot_interval,
+                       "shots_per_gpu_per_step": 1, "sources_per_shot": 2, "receivers": m.nr,
+                       "step": "forward(store)+misfit+adjoint(+kernel accumulation)" + ("+allreduce" if world > 1 else ""),
+                       "parallelism": f"shots x{world}", "variant": m._get_option("variant"),
+                       "exact": m._get_option("exact"),
+                       "l2": f"working set {(8 * nx * nz * 8) >> 20} MiB per sweep > 126 MB L2 (no flush needed)"},
+            "gradient_ms_per_shot": dev_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_value, "unit": "updates/s", "ms_per_step": e2e_ms / args.steps,
+                    "h2d_bytes_per_step": int(sum(a.nbytes for a in host_model)), "d2h_bytes_per_step": grad_bytes},
+            "gpu_launches": int(launches_total),
+            "roofline": roofline,
+        }
+        if cpu:
+            line["cpu_baseline"] = cpu
+        emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+_JSON_OUT = None
+
+
+def emit(line: dict) -> None:
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nt", type=int, default=0, help="override the number of time steps (debug only)")
+    ap.add_argument("--option", action="append", default=[], help="solver option name=value (debug only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    # The solver and the reference print progress lines on stdout (src/fdModel.cpp:396,472);
+    # keep stdout for the ONE JSON line: everything else goes to stderr.
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

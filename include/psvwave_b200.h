@@ -181,9 +181,10 @@ int psv_load_model(psv_handle h, const char *de_path, const char *vp_path, const
 int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, size_t n);
 
 /* ---- additive entry points (not in the reference) ----------------------------------------- */
-/* Drop the stored forward snapshots of one shot (i_shot >= 0) or of all shots (-1).  Lets a
- * per-shot forward->adjoint loop run Marmousi-scale problems whose all-shots snapshot set
- * (src/fdModel.cpp:185-190) would not fit in HBM. */
+/* Drop the stored forward snapshots of one shot (i_shot >= 0): its buffer goes back to the
+ * model's pool and is reused by the next stored forward run.  i_shot = -1 drops all shots and
+ * frees the pool.  Lets a per-shot forward->adjoint loop run Marmousi-scale problems whose
+ * all-shots snapshot set (src/fdModel.cpp:185-190) would not fit in HBM. */
 int psv_release_snapshots(psv_handle h, int i_shot);
 /* L2 misfit of ONE shot (the terms of src/fdModel.cpp:1140-1141 for that shot only); does not
  * touch the stored misfit.  Ranks that own a subset of the shots sum these. */
@@ -193,6 +194,10 @@ int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out);
  * used by the host layer for the cross-rank sum (one all-reduce) over NCCL. */
 int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count);
 int psv_synchronize(psv_handle h);
+/* Device stopwatch on the model's stream (CUDA events): start records an event, stop records a
+ * second one, waits for it and returns the milliseconds between the two. */
+int psv_timer_start(psv_handle h);
+int psv_timer_stop(psv_handle h, double *milliseconds);
 
 /* Tuning / instrumentation knobs, by name.  Unknown names fail with PSV_ERR_INVALID_ARGUMENT.
  *   "variant"  0 = one-thread-per-point kernels, 1 = vectorised x-marching kernels (default)
@@ -201,6 +206,8 @@ int psv_synchronize(psv_handle h);
  *   "profile"  1 = record CUDA events around sampled stencil launches (see psv_get_stat)
  *   "strip", "block"   launch geometry of variant 1 */
 int psv_set_option(psv_handle h, const char *name, long long value);
+/* Number of sweep-kernel variants compiled into the library ("variant" < this). */
+int psv_variant_count(void);
 int psv_get_option(psv_handle h, const char *name, long long *value);
 /* Counters of the last forward/adjoint call:
  *   "elapsed_ms" device time of the whole time loop (CUDA events on the model's stream)

@@ -69,6 +69,8 @@ extern "C" {
 const char *psv_last_error(void) { return g_error.c_str(); }
 const char *psv_version(void) { return "psvwave_b200 0.1 (sm_100a)"; }
 
+int psv_variant_count(void) { return psv::Model::kVariantCount; }
+
 int psv_set_default_device(int device) {
   g_default_device = device;
   return PSV_OK;
@@ -372,6 +374,12 @@ int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count) {
 }
 int psv_synchronize(psv_handle h) {
   return guarded([&] { model(h).synchronize(); });
+}
+int psv_timer_start(psv_handle h) {
+  return guarded([&] { model(h).timer_start(); });
+}
+int psv_timer_stop(psv_handle h, double *milliseconds) {
+  return guarded([&] { *milliseconds = model(h).timer_stop(); });
 }
 int psv_set_option(psv_handle h, const char *name, long long value) {
   return guarded([&] { model(h).set_option(name, value); });

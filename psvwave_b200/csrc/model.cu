@@ -57,6 +57,8 @@ Model::Model(Config cfg, int device) : cfg_(std::move(cfg)), device_(device) {
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
   PSV_CUDA(cudaEventCreate(&ev_end_));
+  PSV_CUDA(cudaEventCreate(&ev_t0_));
+  PSV_CUDA(cudaEventCreate(&ev_t1_));
   allocate();
   initialize_host_tables();
   build_plans();
@@ -68,6 +70,8 @@ Model::~Model() {
   for (cudaEvent_t e : prof_events_) cudaEventDestroy(e);
   if (ev_begin_) cudaEventDestroy(ev_begin_);
   if (ev_end_) cudaEventDestroy(ev_end_);
+  if (ev_t0_) cudaEventDestroy(ev_t0_);
+  if (ev_t1_) cudaEventDestroy(ev_t1_);
   if (stream_) cudaStreamDestroy(stream_);
 }
 
@@ -225,6 +229,8 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
   PSV_CUDA(cudaEventCreate(&ev_end_));
+  PSV_CUDA(cudaEventCreate(&ev_t0_));
+  PSV_CUDA(cudaEventCreate(&ev_t1_));
   allocate();
   t_host_ = o.t_host_;
   stf_host_ = o.stf_host_;
@@ -279,6 +285,20 @@ void Model::synchronize() {
   PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
+void Model::timer_start() {
+  bind();
+  PSV_CUDA(cudaEventRecord(ev_t0_, stream_));
+}
+
+double Model::timer_stop() {
+  bind();
+  PSV_CUDA(cudaEventRecord(ev_t1_, stream_));
+  PSV_CUDA(cudaEventSynchronize(ev_t1_));
+  float ms = 0;
+  PSV_CUDA(cudaEventElapsedTime(&ms, ev_t0_, ev_t1_));
+  return ms;
+}
+
 void Model::check_shot(int i_shot) const {
   if (i_shot < 0 || i_shot >= cfg_.n_shots) throw invalid_argument("Shot index out of range.");
 }
@@ -291,6 +311,12 @@ void Model::zero_dynamic_fields() {
 void Model::ensure_snapshots(int i_shot) {
   DeviceBuffer &s = snapshots_[i_shot];
   const size_t bytes = 5 * (size_t)n_snap_alloc_ * grid_elems_ * sizeof(double);
+  if (s.empty() && !snapshot_pool_.empty()) {
+    // a pooled buffer may hold another shot's snapshots: every snapshot the adjoint reads is
+    // rewritten by the stored forward run, and get_array reports only shots stored since
+    s = std::move(snapshot_pool_.back());
+    snapshot_pool_.pop_back();
+  }
   if (s.empty()) {
     try {
       s.allocate(bytes);
@@ -315,9 +341,11 @@ void Model::release_snapshots(int i_shot) {
   PSV_CUDA(cudaStreamSynchronize(stream_));
   if (i_shot < 0) {
     for (DeviceBuffer &s : snapshots_) s.release();
+    snapshot_pool_.clear();
   } else {
     check_shot(i_shot);
-    snapshots_[i_shot].release();
+    if (!snapshots_[i_shot].empty()) snapshot_pool_.push_back(std::move(snapshots_[i_shot]));
+    snapshots_[i_shot] = DeviceBuffer();
   }
 }
 
@@ -993,7 +1021,7 @@ void Model::load_vector(const std::string &path, bool verbose, double *out, size
 // ---------------------------------------------------------------------------------------------
 void Model::set_option(const std::string &name, long long v) {
   if (name == "variant") {
-    if (v < 0 || v > 1) throw invalid_argument("variant must be 0 or 1");
+    if (v < 0 || v >= kVariantCount) throw invalid_argument("variant out of range");
     variant_ = (int)v;
   } else if (name == "exact") {
     exact_ = v != 0;

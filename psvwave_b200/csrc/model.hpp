@@ -67,6 +67,7 @@ struct GridArray {
 
 class Model {
  public:
+  static constexpr int kVariantCount = 2;
   explicit Model(Config cfg, int device);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -105,6 +106,8 @@ class Model {
   void release_snapshots(int i_shot);
   void kernel_buffer(void **ptr, size_t *count) const;
   void synchronize();
+  void timer_start();
+  double timer_stop();
 
   void set_option(const std::string &name, long long value);
   long long get_option(const std::string &name) const;
@@ -137,7 +140,7 @@ class Model {
   Config cfg_;
   int device_ = 0;
   cudaStream_t stream_ = nullptr;
-  cudaEvent_t ev_begin_ = nullptr, ev_end_ = nullptr;
+  cudaEvent_t ev_begin_ = nullptr, ev_end_ = nullptr, ev_t0_ = nullptr, ev_t1_ = nullptr;
   std::vector<cudaEvent_t> prof_events_;
 
   // geometry of the device layout
@@ -162,6 +165,7 @@ class Model {
   int n_rec_heads_ = 0;
   std::vector<ShotPlan> plans_;
   std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
+  std::vector<DeviceBuffer> snapshot_pool_;  // released buffers, reused by ensure_snapshots
   DeviceBuffer scratch_;                 // reduction partials / vectors
 
   double misfit_ = 0.0;

@@ -257,6 +257,13 @@ class FdModel {
     check(psv_get_stat(h_, name.c_str(), &v));
     return v;
   }
+  void timer_start() { check(psv_timer_start(h_)); }
+  double timer_stop() {
+    double ms = 0;
+    check(psv_timer_stop(h_, &ms));
+    return ms;
+  }
+  void synchronize() { check(psv_synchronize(h_)); }
   py::tuple device_kernel_buffer() const {
     void *p = nullptr;
     size_t n = 0;
@@ -278,6 +285,7 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
     check(psv_device_count(&n));
     return n;
   });
+  m.def("max_variant", [] { return psv_variant_count() - 1; });
   m.def("version", [] { return std::string(psv_version()); });
 
 #define RO_INT(name, key) def_property_readonly(name, [](const FdModel &s) { return s.geti(key); })
@@ -351,5 +359,8 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       .def("_set_option", &FdModel::set_option)
       .def("_get_option", &FdModel::get_option)
       .def("_get_stat", &FdModel::get_stat)
+      .def("_timer_start", &FdModel::timer_start)
+      .def("_timer_stop", &FdModel::timer_stop)
+      .def("synchronize", &FdModel::synchronize)
       .def("_device_kernel_buffer", &FdModel::device_kernel_buffer);
 }

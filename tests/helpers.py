@@ -75,3 +75,35 @@ def ragged_config(path, **extra):
                 snapshot_interval=6, npx=3, npz=9, delay_cycles_per_shot=2, dt=0.00025)
     base.update(extra)
     return make_config(path, **base)
+
+
+def array_ids():
+    """psv_array enumerators of include/psvwave_b200.h -> {reference field name: id}."""
+    import re
+    text = open(os.path.join(ROOT, "include", "psvwave_b200.h")).read()
+    body = re.search(r"typedef enum psv_array \{(.*?)\} psv_array;", text, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = [n.strip().split("=")[0].strip() for n in body.split(",") if n.strip()]
+    out = {}
+    for i, n in enumerate(names):
+        key = n[len("PSV_"):].lower()
+        key = {"rtf_ux_true": "rtf_ux_true", "rtf_uz_true": "rtf_uz_true"}.get(key, key)
+        out[key] = i
+    return out
+
+
+def gpu_array(m, name):
+    """Any internal array of the CUDA model, shaped like the reference's (src/fdModel.h:209-252)."""
+    ids = array_ids()
+    flat = m._get_array(ids[name])
+    if name in ("t",):
+        return flat
+    if name == "stf":
+        return flat.reshape(m.n_sources, m.nt)
+    if name == "moment":
+        return flat.reshape(m.n_sources, 2, 2)
+    if name.startswith(("rtf_", "a_stf_")):
+        return flat.reshape(m.n_shots, m.nr, m.nt)
+    if name.startswith("accu_"):
+        return flat.reshape(m.n_shots, m.snapshots, m.nx, m.nz)
+    return flat.reshape(m.nx, m.nz)

@@ -1,0 +1,224 @@
+"""Parity of the CUDA path (psvwave_b200.fdModel -> C ABI -> sm_100a kernels) against
+  (1) the committed golden vectors produced by the UNMODIFIED reference core,
+  (2) the known answers printed in the reference's notebook 2,
+  (3) the CPU oracle (oracle/psv_oracle.c, itself pinned bit-exact to the reference) on fresh
+      seeded ragged inputs.
+Tolerances: the default arithmetic ("exact" = 0: reciprocal multiplies + FMA contraction) must
+agree within TOL = 1e-10 relative L2 (north_star); with "exact" = 1 (IEEE operation order of
+the reference) every array must be BIT-IDENTICAL.
+"""
+import numpy as np
+import pytest
+
+from conftest import SMALL_INI, rel_l2
+from helpers import C1_INI, DYNAMIC, gpu_array, gradient_workflow, notebook2_models, ragged_config, random_medium
+from oracle.oracle import OracleModel
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-10  # relative L2, FP64 (BASELINE.json north_star)
+
+KERNELS = ("lambda_kernel", "mu_kernel", "density_l_kernel", "vp_kernel", "vs_kernel", "density_v_kernel")
+
+
+def fd(ini, **options):
+    import psvwave_b200
+    m = psvwave_b200.fdModel(ini)
+    for k, v in options.items():
+        m._set_option(k, v)
+    return m
+
+
+def close(a, b, what, exact):
+    if exact:
+        assert np.array_equal(a, b), f"{what}: not bit-identical (rel L2 {rel_l2(a, b):.3e})"
+    else:
+        e = rel_l2(a, b)
+        assert e <= TOL, f"{what}: rel L2 {e:.3e} > {TOL}"
+
+
+VARIANTS = [dict(variant=0, exact=1), dict(variant=0, exact=0), dict(variant=1, exact=1), dict(variant=1, exact=0),
+            dict(variant=2, exact=1), dict(variant=2, exact=0)]
+
+
+def variant_id(o):
+    return f"v{o['variant']}-{'exact' if o['exact'] else 'fast'}"
+
+
+def supported(m_opts):
+    import psvwave_b200
+    return m_opts["variant"] <= psvwave_b200.max_variant()
+
+
+@pytest.mark.parametrize("opts", VARIANTS, ids=variant_id)
+def test_small_multishot_vs_reference_golden(golden, opts):
+    if not supported(opts):
+        pytest.skip("variant not built")
+    g = golden("small_multishot")
+    exact = bool(opts["exact"])
+    m = fd(SMALL_INI, **opts)
+    for name in ("taper", "stf", "moment"):  # host tables: always bit-identical
+        assert np.array_equal(gpu_array(m, name), g[name]), name
+    m.set_parameter_fields(g["vp"], g["vs"], g["rho"])
+    for name in ("lm", "la", "mu", "b_vx", "b_vz"):
+        assert np.array_equal(gpu_array(m, name), g[name if name != "b_vz" else "b_vx"]), name
+    for s in range(m.n_shots):
+        m.forward_simulate(s, True)
+    ux, uz = m.get_synthetic_data()
+    close(ux, g["ux"], "ux", exact)
+    close(uz, g["uz"], "uz", exact)
+    snaps = m.get_snapshots()
+    for f, a in zip(DYNAMIC, snaps):
+        assert a.shape == (m.n_shots, m.snapshots, m.nx, m.nz)
+        close(a[:, [0, 17, 60]], g["snap_" + f], "snapshot " + f, exact)
+        close(gpu_array(m, f), g["fwd_end_" + f], "final " + f, exact)
+    assert np.array_equal(m.get_model_vector(), g["model_vector"])
+    m.set_observed_data(g["obs_ux"], g["obs_uz"])
+    gradient_workflow(m)
+    if exact:
+        assert abs(m.misfit - float(g["misfit"])) <= 1e-14 * float(g["misfit"])  # summation order differs
+    else:
+        assert abs(m.misfit - float(g["misfit"])) <= TOL * float(g["misfit"])
+    for name in ("a_stf_ux", "a_stf_uz") + KERNELS:
+        close(gpu_array(m, name), g[name], name, exact)
+    close(m.get_gradient_vector(), g["gradient"], "gradient", exact)
+    close(gpu_array(m, "vx"), g["adj_end_vx"], "adjoint final vx", exact)
+    close(gpu_array(m, "txx"), g["adj_end_txx"], "adjoint final txx", exact)
+
+
+@pytest.fixture(scope="module")
+def c1_gpu_run():
+    """Default configuration (configs[0]): homogeneous forward, then the notebook-2 gradient."""
+    m = fd(C1_INI)
+    m.forward_simulate(0, True)
+    ux, uz = m.get_synthetic_data()
+    snaps = m.get_snapshots()
+    homog = dict(ux=ux, uz=uz, snap_vx=snaps[0][0, 400].copy(), snap_txz=snaps[4][0, 400].copy(),
+                 final_vx=gpu_array(m, "vx"), final_tzz=gpu_array(m, "tzz"), taper=gpu_array(m, "taper"),
+                 stf=gpu_array(m, "stf"), moment=gpu_array(m, "moment"),
+                 snapnorms={(f, k): np.linalg.norm(snaps[i][0, k]) for i, f in enumerate(DYNAMIC)
+                            for k in (100, 400, 799)})
+    del snaps
+    start, target = notebook2_models(m)
+    m.set_parameter_fields(*target)
+    m.forward_simulate(0, True)
+    obs = m.get_synthetic_data()
+    m.set_observed_data(*obs)
+    m.set_parameter_fields(*start)
+    gradient_workflow(m)
+    return homog, obs, m
+
+
+def test_c1_homogeneous_vs_reference_golden(golden, c1_gpu_run):
+    g = golden("c1_homogeneous")
+    h = c1_gpu_run[0]
+    close(h["ux"][:, :, ::8], g["ux_dec8"], "ux", False)
+    close(h["uz"][:, :, ::8], g["uz_dec8"], "uz", False)
+    assert np.linalg.norm(h["ux"]) == pytest.approx(float(g["norm_ux"]), rel=TOL)
+    assert np.linalg.norm(h["uz"]) == pytest.approx(float(g["norm_uz"]), rel=TOL)
+    # SURVEY 8(c)-3 scalars probed from the compiled reference
+    assert np.linalg.norm(h["ux"]) == pytest.approx(150626.52785852677, rel=TOL)
+    assert np.linalg.norm(h["uz"]) == pytest.approx(99534.43907778655, rel=TOL)
+    assert h["ux"].sum() == pytest.approx(-21.249427595741352, rel=1e-8)  # cancelling sum
+    close(h["snap_vx"][::3, ::3], g["snap_vx_400_dec"], "snapshot vx[400]", False)
+    close(h["snap_txz"][::3, ::3], g["snap_txz_400_dec"], "snapshot txz[400]", False)
+    close(h["final_vx"][::3, ::3], g["final_vx_dec"], "final vx", False)
+    close(h["final_tzz"][::3, ::3], g["final_tzz_dec"], "final tzz", False)
+    assert np.array_equal(h["taper"][:, 75], g["taper_row"])
+    assert np.array_equal(h["stf"][:, ::16], g["stf_dec"])
+    assert np.array_equal(h["moment"], g["moment"])
+    for (f, k), v in h["snapnorms"].items():
+        assert v == pytest.approx(float(g[f"snapnorm_{f}_{k}"]), rel=TOL)
+
+
+def test_c1_notebook2_known_answers(golden, c1_gpu_run):
+    g = golden("c1_notebook2")
+    _, obs, m = c1_gpu_run
+    # what the reference's own notebook prints (notebooks/Notebook 2 ...ipynb:240,443)
+    assert f"{m.misfit:.2f}" == "1920401.82"
+    grad = m.get_gradient_vector()
+    assert f"{np.abs(grad).max():.5E}" == "7.71590E+01"
+    # what the compiled reference gives
+    assert m.misfit == pytest.approx(float(g["misfit"]), rel=TOL)
+    close(grad[::7], g["g_dec7"], "gradient", False)
+    assert np.linalg.norm(grad) == pytest.approx(float(g["g_norm"]), rel=TOL)
+    close(obs[0][:, :, ::8], g["obs_ux_dec8"], "observed ux", False)
+    close(obs[1][:, :, ::8], g["obs_uz_dec8"], "observed uz", False)
+    for name in ("lambda_kernel", "mu_kernel", "density_l_kernel", "vs_kernel"):
+        close(gpu_array(m, name)[::3, ::3], g[name + "_dec"], name, False)
+    absmax = np.array([np.abs(k).max() for k in m.get_kernels()])
+    assert np.allclose(absmax, g["kernel_absmax"], rtol=TOL, atol=0)
+
+
+def _ragged_pair(tmp_path, opts, **extra):
+    ini = str(tmp_path / "ragged.ini")
+    ragged_config(ini, **extra)
+    o, m = OracleModel(ini), fd(ini, **opts)
+    vp, vs, rho = random_medium(o.nx, o.nz, seed=7)
+    for x in (o, m):
+        x.set_parameter_fields(vp, vs, rho)
+        for s in range(x.n_shots):
+            x.forward_simulate(s, True)
+    obs = [a * f for a, f in zip(o.get_synthetic_data(), (1.05, 0.95))]
+    for x in (o, m):
+        x.set_observed_data(*obs)
+        gradient_workflow(x)
+    return o, m
+
+
+@pytest.mark.parametrize("opts", VARIANTS, ids=variant_id)
+def test_ragged_case_vs_oracle(tmp_path, opts):
+    """Odd grid sizes, 3 shots with 2/1/1 sources, coinciding receivers, receiver next to a
+    source, basis blocks 3x9, random medium -- every array of the path."""
+    if not supported(opts):
+        pytest.skip("variant not built")
+    exact = bool(opts["exact"])
+    o, m = _ragged_pair(tmp_path, opts)
+    for name in ("taper", "stf", "moment", "lm", "la", "mu", "b_vx", "b_vz", "vp", "vs", "rho"):
+        assert np.array_equal(gpu_array(m, name), o.array(name)), name
+    for name in ("rtf_ux", "rtf_uz", "a_stf_ux", "a_stf_uz", "accu_vx", "accu_vz", "accu_txx", "accu_tzz",
+                 "accu_txz", "vx", "vz", "txx", "tzz", "txz") + KERNELS:
+        close(gpu_array(m, name), o.array(name), name, exact)
+    assert m.misfit == pytest.approx(o.misfit, rel=1e-14 if exact else TOL)
+    close(m.get_gradient_vector(), o.get_gradient_vector(), "gradient", exact)
+    assert np.array_equal(m.get_model_vector(), o.get_model_vector())
+    v = o.get_model_vector() * 1.01
+    o.set_model_vector(v)
+    m.set_model_vector(v)
+    for name in ("vp", "vs", "rho", "lm", "la", "mu", "b_vx"):
+        assert np.array_equal(gpu_array(m, name), o.array(name)), name
+
+
+@pytest.mark.parametrize("nz_inner,nx_inner", [(17, 21), (30, 19), (115, 64), (257, 40)])
+def test_grid_shapes_vs_oracle(tmp_path, nz_inner, nx_inner):
+    """Row lengths around the vector width / pitch / tile boundaries of the sweeps."""
+    extra = dict(nx_inner=nx_inner, nz_inner=nz_inner, nt=90, nx_inner_boundary=2, nz_inner_boundary=2,
+                 np_boundary=5, npx=1, npz=1, n_sources=2, n_shots=1, ix_sources=[3, nx_inner - 3],
+                 iz_sources=[4, nz_inner - 4], moment_angles=[10.0, 200.0],
+                 which_source_to_fire_in_which_shot=[[0, 1]], nr=3, ix_receivers=[2, nx_inner // 2, nx_inner - 2],
+                 iz_receivers=[2, nz_inner // 2, nz_inner - 2], snapshot_interval=9, delay_cycles_per_shot=0.5)
+    import psvwave_b200
+    for variant in range(psvwave_b200.max_variant() + 1):
+        o, m = _ragged_pair(tmp_path, dict(variant=variant, exact=1), **extra)
+        for name in ("rtf_ux", "rtf_uz", "accu_vx", "accu_txz", "vx", "vz", "txx", "tzz", "txz") + KERNELS:
+            close(gpu_array(m, name), o.array(name), f"variant {variant} {name}", True)
+
+
+def test_forward_without_store_and_state_errors(tmp_path):
+    ini = str(tmp_path / "r.ini")
+    ragged_config(ini)
+    m = fd(ini)
+    m.forward_simulate(1, False)
+    a = m.get_synthetic_data()[0][1].copy()
+    with pytest.raises(RuntimeError):  # no stored forward field for this shot
+        m.adjoint_simulate(1)
+    m.forward_simulate(1, True)
+    assert np.array_equal(m.get_synthetic_data()[0][1], a)  # determinism (tests/test_file_constructor.cpp:59-68)
+    with pytest.raises(ValueError):
+        m.forward_simulate(7)
+    with pytest.raises(ValueError):
+        m.set_parameter_fields(np.ones((3, 3)), np.ones((3, 3)), np.ones((3, 3)))
+    with pytest.raises(ValueError):
+        m.set_observed_data(np.ones((1, 2, 3)), np.ones((1, 2, 3)))
+    with pytest.raises(ValueError):
+        m.set_model_vector(np.ones(5))
