@@ -177,8 +177,8 @@ def big(tmp_path_factory):
     nxi, nzi = 1200, 700
     make_config(ini, nt=300, nx_inner=nxi, nz_inner=nzi, nx_inner_boundary=20, nz_inner_boundary=20,
                 np_boundary=40, np_factor=0.0075, dx=2.5, dz=2.5, dt=2.5e-4, peak_frequency=12.0,
-                n_sources=3, n_shots=3, ix_sources=[300, 600, 900], iz_sources=[30, 350, 30],
-                moment_angles=[90.0, 45.0, 0.0], which_source_to_fire_in_which_shot=[[0], [1], [0, 1]],
+                n_sources=4, n_shots=3, ix_sources=[300, 600, 300, 600], iz_sources=[30, 350, 30, 350],
+                moment_angles=[90.0, 45.0, 90.0, 45.0], which_source_to_fire_in_which_shot=[[0], [1], [2, 3]],
                 nr=40, ix_receivers=list(range(100, 1100, 25)), iz_receivers=[20] * 40,
                 snapshot_interval=20, delay_cycles_per_shot=0.0, npx=1, npz=1)
     return ini
@@ -202,7 +202,8 @@ def test_big_variants_agree_and_superpose(big):
         assert np.array_equal(ux, ux0) and np.array_equal(uz, uz0)
         for f in ("vx", "txz"):
             assert np.array_equal(gpu_array(m, f), gpu_array(ms[0], f))
-    # linearity: shot 2 fires sources 0 and 1 together (no delay) = shot 0 + shot 1
+    # linearity: shot 2 fires copies of sources 0 and 1 together (no delay) = shot 0 + shot 1
+    # (the reference requires every source to be listed exactly once, src/fdModel.cpp:433-441)
     assert rel_l2(ux0[0] + ux0[1], ux0[2]) < 1e-12
     assert rel_l2(uz0[0] + uz0[1], uz0[2]) < 1e-12
     # default arithmetic vs IEEE-order arithmetic at scale
