@@ -28,6 +28,7 @@ void DeviceBuffer::allocate(size_t bytes) {
   PSV_CUDA(cudaMalloc(&p_, bytes));
   bytes_ = bytes;
   PSV_CUDA(cudaMemset(p_, 0, bytes));
+  PSV_CUDA(cudaStreamSynchronize(cudaStreamLegacy));  // the model's stream does not order against the legacy stream
 }
 
 void DeviceBuffer::release() {
@@ -123,8 +124,7 @@ void Model::initialize_host_tables() {
       }
     }
   }
-  PSV_CUDA(cudaMemcpy(stf_.as<>(), stf_host_.data(), stf_host_.size() * sizeof(double),
-                      cudaMemcpyHostToDevice));
+  copy_sync(stf_.as<>(), stf_host_.data(), stf_host_.size() * sizeof(double), cudaMemcpyHostToDevice);
   // moment tensors (src/fdModel.cpp:234-246)
   moment_host_.assign((size_t)c.n_sources * 4, 0.0);
   for (int s = 0; s < c.n_sources; ++s) {
@@ -140,15 +140,14 @@ void Model::initialize_host_tables() {
     const double cnt = (double)n;
     taper_host_[n] = std::exp(-std::pow(c.np_factor * (c.np_boundary - cnt), 2));
   }
-  PSV_CUDA(cudaMemcpy(taper_table_.as<>(), taper_host_.data(), taper_host_.size() * sizeof(double),
-                      cudaMemcpyHostToDevice));
+  copy_sync(taper_table_.as<>(), taper_host_.data(), taper_host_.size() * sizeof(double), cudaMemcpyHostToDevice);
   // homogeneous medium (src/fdModel.cpp:249-261); pad columns get the same values so that
   // 1/rho stays finite everywhere.
   std::vector<double> fill(grid_elems_);
   const std::pair<GridArray *, double> scal[] = {{&vp_, c.scalar_vp}, {&vs_, c.scalar_vs}, {&rho_, c.scalar_rho}};
   for (const auto &p : scal) {
     std::fill(fill.begin(), fill.end(), p.second);
-    PSV_CUDA(cudaMemcpy(p.first->data(), fill.data(), grid_elems_ * sizeof(double), cudaMemcpyHostToDevice));
+    copy_sync(p.first->data(), fill.data(), grid_elems_ * sizeof(double), cudaMemcpyHostToDevice);
   }
   update_from_velocity();
 }
@@ -170,9 +169,9 @@ void Model::build_plans() {
   rec_index_.allocate(idx.size() * sizeof(int));
   rec_next_.allocate(next.size() * sizeof(int));
   rec_heads_.allocate(heads.size() * sizeof(int));
-  PSV_CUDA(cudaMemcpy(rec_index_.as<int>(), idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice));
-  PSV_CUDA(cudaMemcpy(rec_next_.as<int>(), next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice));
-  PSV_CUDA(cudaMemcpy(rec_heads_.as<int>(), heads.data(), heads.size() * sizeof(int), cudaMemcpyHostToDevice));
+  copy_sync(rec_index_.as<int>(), idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice);
+  copy_sync(rec_next_.as<int>(), next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice);
+  copy_sync(rec_heads_.as<int>(), heads.data(), heads.size() * sizeof(int), cudaMemcpyHostToDevice);
 
   // sources: the 12 point updates per source in the order of src/fdModel.cpp:702-750
   const double dx4 = c.dx * c.dx * c.dx * c.dx, dz4 = c.dz * c.dz * c.dz * c.dz;
@@ -218,8 +217,8 @@ void Model::build_plans() {
     if (ops.empty()) continue;
     p.ops.allocate(ops.size() * sizeof(InjectOp));
     p.heads.allocate(op_heads.size() * sizeof(int));
-    PSV_CUDA(cudaMemcpy(p.ops.as<InjectOp>(), ops.data(), ops.size() * sizeof(InjectOp), cudaMemcpyHostToDevice));
-    PSV_CUDA(cudaMemcpy(p.heads.as<int>(), op_heads.data(), op_heads.size() * sizeof(int), cudaMemcpyHostToDevice));
+    copy_sync(p.ops.as<InjectOp>(), ops.data(), ops.size() * sizeof(InjectOp), cudaMemcpyHostToDevice);
+    copy_sync(p.heads.as<int>(), op_heads.data(), op_heads.size() * sizeof(int), cudaMemcpyHostToDevice);
   }
 }
 
@@ -246,7 +245,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
     if (src.empty()) return;
     if (dst.bytes() != src.bytes()) dst.allocate(src.bytes());
-    PSV_CUDA(cudaMemcpy(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice));
+    copy_sync(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice);
   };
   const GridArray *gs[] = {&o.vx_, &o.vz_, &o.txx_, &o.tzz_, &o.txz_, &o.vp_, &o.vs_, &o.rho_, &o.lm_,
                            &o.mu_, &o.b_, &o.vp_kernel_, &o.vs_kernel_, &o.density_v_kernel_};
@@ -271,13 +270,25 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
 // host <-> device helpers
 // ---------------------------------------------------------------------------------------------
 void Model::grid_to_host(const double *dev, double *host) const {
-  PSV_CUDA(cudaMemcpy2D(host, cfg_.nz * sizeof(double), dev, ld_ * sizeof(double),
-                        cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyDeviceToHost));
+  PSV_CUDA(cudaMemcpy2DAsync(host, cfg_.nz * sizeof(double), dev, ld_ * sizeof(double),
+                             cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
 void Model::grid_from_host(double *dev, const double *host) const {
-  PSV_CUDA(cudaMemcpy2D(dev, ld_ * sizeof(double), host, cfg_.nz * sizeof(double),
-                        cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyHostToDevice));
+  // stream-ordered: a plain cudaMemcpy2D from pageable memory may return before the DMA lands,
+  // and the model's non-blocking stream would not wait for it
+  PSV_CUDA(cudaMemcpy2DAsync(dev, ld_ * sizeof(double), host, cfg_.nz * sizeof(double),
+                             cfg_.nz * sizeof(double), cfg_.nx, cudaMemcpyHostToDevice, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+// Copy on the model's stream and wait for it (every buffer of a model is only ever touched
+// on that stream, so this is the one ordering domain).
+void Model::copy_sync(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind) const {
+  if (bytes == 0) return;
+  PSV_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
 void Model::synchronize() {
@@ -775,7 +786,7 @@ void Model::get_array(psv_array which, double *out, size_t count) {
     case PSV_A_STF_UX:
     case PSV_A_STF_UZ: {
       const DeviceBuffer *b[] = {&rtf_ux_, &rtf_uz_, &obs_ux_, &obs_uz_, &a_stf_ux_, &a_stf_uz_};
-      if (count) PSV_CUDA(cudaMemcpy(out, b[which - PSV_RTF_UX]->as<>(), count * sizeof(double), cudaMemcpyDeviceToHost));
+      if (count) copy_sync(out, b[which - PSV_RTF_UX]->as<>(), count * sizeof(double), cudaMemcpyDeviceToHost);
       return;
     }
     case PSV_ACCU_VX:
@@ -790,8 +801,10 @@ void Model::get_array(psv_array which, double *out, size_t count) {
         if (snapshots_[s].empty() || per_shot == 0) {
           std::memset(dst, 0, per_shot * sizeof(double));
         } else {
-          PSV_CUDA(cudaMemcpy2D(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
-                                c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost));
+          PSV_CUDA(cudaMemcpy2DAsync(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
+                                     c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost,
+                                     stream_));
+          PSV_CUDA(cudaStreamSynchronize(stream_));
         }
       }
       return;
@@ -814,7 +827,7 @@ void Model::set_array(psv_array which, const double *in, size_t count) {
     case PSV_DENSITY_L_KERNEL: return grid_from_host(k + 2 * grid_elems_, in);
     case PSV_STF:
       stf_host_.assign(in, in + count);
-      if (count) PSV_CUDA(cudaMemcpy(stf_.as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice));
+      if (count) copy_sync(stf_.as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice);
       return;
     case PSV_MOMENT:
       moment_host_.assign(in, in + count);
@@ -827,7 +840,7 @@ void Model::set_array(psv_array which, const double *in, size_t count) {
     case PSV_A_STF_UX:
     case PSV_A_STF_UZ: {
       DeviceBuffer *b[] = {&rtf_ux_, &rtf_uz_, &obs_ux_, &obs_uz_, &a_stf_ux_, &a_stf_uz_};
-      if (count) PSV_CUDA(cudaMemcpy(b[which - PSV_RTF_UX]->as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice));
+      if (count) copy_sync(b[which - PSV_RTF_UX]->as<>(), in, count * sizeof(double), cudaMemcpyHostToDevice);
       return;
     }
     default: throw invalid_argument("This array cannot be set.");

@@ -126,6 +126,7 @@ class Model {
   void build_plans();
   void bind() const;  // cudaSetDevice
   GridArray make_grid() const;
+  void copy_sync(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind) const;
   void grid_to_host(const double *dev, double *host) const;
   void grid_from_host(double *dev, const double *host) const;
   void zero_dynamic_fields();
