@@ -1,0 +1,478 @@
+// Variant 2: ONE launch per time step.
+//
+// The stress sweep (src/fdModel.cpp:599-644 / :864-911), the velocity sweep (:646-678 /
+// :913-948), the snapshot store (:555-572), the sensitivity-kernel accumulation (:817-861),
+// receiver sampling (:576-596), moment-tensor injection (:681-751) and adjoint-source
+// injection (:951-958) of one time step in a single pass over the grid:
+//     reads  vx vz txx tzz txz (old state) + lm mu b            8 words / point
+//     writes vx vz txx tzz txz (new state, ping-pong buffers)   5 words / point
+// = 104 B per grid-point update against 144 B for the two-sweep variant (176 B algorithmic
+// with la, b_vz and the taper array the reference streams).
+//
+// Work decomposition: a WARP owns 28 z-pairs (56 grid columns) of a strip of rows and marches
+// along x.  Lanes 0,1 and 30,31 carry the z-halo: lane l holds pair 28*zw - 2 + l.  The old
+// velocities of rows j-2..j+2 and the NEW stresses of rows j-4..j ride in rolling register
+// windows, so each row costs exactly one coalesced 16-byte load per array and lane;
+// z-neighbours (old velocities for the stress update, new stresses for the velocity update)
+// come from the adjacent lanes by warp shuffle.  Row j's stresses are updated first, the
+// velocities of row j-2 -- whose x-operators need new stresses up to row j -- right after.
+// No shared memory, no block barrier; warps are fully independent.  The state is
+// double-buffered (read `old`, write `new`) because neighbouring warps/strips recompute the
+// halo from the old state: strips overlap by 4 stress rows, warps by 2 pairs on each side.
+//
+// Point operations ride along: receivers and injection operations are bucketed by grid row
+// (CSR over ix, original order kept inside a row), and the lane that owns the target point
+// applies them -- sampling from the old velocities it holds, injections on the freshly
+// updated velocities before they are stored -- in the reference's sequence, with the same
+// explicitly rounded operations as the stand-alone point kernels (pointwise.cuh).
+//
+// Batched launches (Monte-Carlo ensembles): blockIdx.z selects one FusedModel (the per-model
+// pointers); geometry, point-operation lists and the time index are shared by the batch.
+#pragma once
+
+#include "kernels.cuh"
+#include "pointwise.cuh"
+
+namespace psv {
+
+constexpr int kFusedOwnedPairs = 28;  // lanes 2..29 of a warp
+
+// Injection operation bucketed by row (sorted by target row, original order kept).
+struct RowOp {
+  int z;          // target column
+  int field;      // 0 = vx, 1 = vz
+  int source;     // row of stf
+  int pad;
+  double weight;  // moment entry (x0.25 where the reference does)
+  double sign;    // +1 / -1
+  double d4;      // dx^4 or dz^4
+};
+
+enum PointMode { POINT_NONE = 0, POINT_FORWARD = 1, POINT_ADJOINT = 2 };
+
+struct FusedModel {  // per-model pointers (constant during one simulate call)
+  double *f[2][5];   // ping-pong state: [parity][vx vz txx tzz txz]
+  const double *lm, *mu, *b;
+  double *snap;      // this shot's snapshots [5][n_snap_alloc][nx*ld]
+  double *k_lam, *k_mu, *k_rho;
+  double *ux, *uz;        // synthetics of this shot [nr][nt]      (POINT_FORWARD)
+  const double *ax, *az;  // adjoint sources of this shot [nr][nt] (POINT_ADJOINT)
+};
+
+struct FusedCommon {
+  GridShape g;
+  SweepConsts k;
+  const double *taper_table;
+  int parity;       // old state = f[parity], new state = f[parity ^ 1]
+  int n_zwarps;     // ceil(ld/2 / 28)
+  int strip;        // rows per warp
+  // snapshots / kernel accumulation
+  size_t snap_field_stride;  // n_snap_alloc * nx*ld
+  size_t snap_offset;        // snapshot index * nx*ld
+  int wx0, wx1, wz0, wz1;
+  double sidt;
+  // point operations
+  int point_mode;
+  int nt, it;
+  double dt, dxdz;
+  const int *rec_row_start;  // [nx+1] CSR over rows of the receivers sorted by (ix, r)
+  const int *rec_z;          // column of sorted receiver q
+  const int *rec_id;         // original receiver number of sorted receiver q
+  const int *op_row_start;   // [nx+1] CSR over rows of this shot's injection operations
+  const RowOp *ops;
+  const double *stf;         // [n_sources][nt]
+};
+
+__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double2 ld2s(const double *p, long long pair) {
+  return __ldg(reinterpret_cast<const double2 *>(p) + pair);
+}
+__device__ __forceinline__ void st2s(double *p, long long pair, double2 v) {
+  *(reinterpret_cast<double2 *>(p) + pair) = v;
+}
+
+// The 8 double2 a lane needs for one iteration of the march (row j; velocities of row j-2).
+struct RowData {
+  double2 vx_p2, vz_p1;   // old vx row j+2, old vz row j+1
+  double2 txx, tzz, txz;  // old stresses row j
+  double2 lm, mu;         // medium row j
+  double2 b;              // 1/rho row j-2
+};
+
+// Row source of variant 2: straight from global memory (read-only path).
+struct GlobalRows {
+  const double *ovx, *ovz, *oxx, *ozz, *oxz, *lm, *mu, *b;
+  long long ld2n;
+  __device__ __forceinline__ void fetch(long long r, RowData &d) const {
+    d.vx_p2 = ld2s(ovx, r + 2 * ld2n);
+    d.vz_p1 = ld2s(ovz, r + ld2n);
+    d.txx = ld2s(oxx, r);
+    d.tzz = ld2s(ozz, r);
+    d.txz = ld2s(oxz, r);
+    d.lm = ld2s(lm, r);
+    d.mu = ld2s(mu, r);
+    d.b = ld2s(b, r - 2 * ld2n);
+  }
+};
+
+// One warp marches rows [xs, xe) for the z-pairs {kp0 + lane}; lanes 2..29 own their pair.
+template <class M, int MODE, class Rows>
+__device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedModel &m, Rows &rows,
+                                            const int lane, const int kp, const int xs, const int xe) {
+  const int nx = c.g.nx, nz = c.g.nz;
+  const long long ld2n = c.g.ld >> 1;
+  const int z0 = kp * 2;
+  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
+  const bool za = z0 >= 2 && z0 < nz - 2;
+  const bool zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
+
+  const double *__restrict__ ovx = m.f[c.parity][0], *__restrict__ ovz = m.f[c.parity][1];
+  double *__restrict__ nvx = m.f[c.parity ^ 1][0], *__restrict__ nvz = m.f[c.parity ^ 1][1];
+  double *__restrict__ nxx = m.f[c.parity ^ 1][2], *__restrict__ nzz = m.f[c.parity ^ 1][3];
+  double *__restrict__ nxz = m.f[c.parity ^ 1][4];
+
+  // point operations present in this strip?
+  bool strip_rec = false, strip_ops = false;
+  if (c.point_mode != POINT_NONE) {
+    strip_rec = c.rec_row_start[xe] > c.rec_row_start[xs];
+    if (c.point_mode == POINT_FORWARD) strip_ops = c.op_row_start[xe] > c.op_row_start[xs];
+  }
+
+  // j = row whose stresses are updated in this iteration; velocities of row j-2 follow.
+  int j = xs - 2;
+  long long r = (long long)j * ld2n + kp;
+  // old velocities: vx rows j-2..j+1 (+ j+2 loaded per iteration), vz rows j-2..j (+ j+1)
+  double2 vx_m2 = ld2s(ovx, r - 2 * ld2n), vx_m1 = ld2s(ovx, r - ld2n), vx_0 = ld2s(ovx, r),
+          vx_p1 = ld2s(ovx, r + ld2n);
+  double2 vz_m2 = ld2s(ovz, r - 2 * ld2n), vz_m1 = ld2s(ovz, r - ld2n), vz_0 = ld2s(ovz, r);
+  // new stresses: txx rows j-4..j-1, txz rows j-3..j-1, tzz rows j-2..j-1
+  const double2 zero2 = make_double2(0.0, 0.0);
+  double2 xx_m4 = zero2, xx_m3 = zero2, xx_m2 = zero2, xx_m1 = zero2;
+  double2 xz_m3 = zero2, xz_m2 = zero2, xz_m1 = zero2;
+  double2 zz_m2 = zero2, zz_m1 = zero2;
+
+#pragma unroll 1
+  for (; j < xe + 2; ++j, r += ld2n) {
+    RowData d;
+    rows.fetch(r, d);
+    const double2 vx_p2 = d.vx_p2, vz_p1 = d.vz_p1;
+    double2 txx = d.txx, tzz = d.tzz, txz = d.txz;
+    const double2 lm = d.lm, mu = d.mu;
+    const bool row_mine = j >= xs && j < xe;  // warp-uniform
+
+    if (row_mine) {
+      if (MODE == MODE_SNAPSHOT && own) {
+        double *s = m.snap + c.snap_offset;
+        st2s(s, r, vx_0);
+        st2s(s + c.snap_field_stride, r, vz_0);
+        st2s(s + 2 * c.snap_field_stride, r, txx);
+        st2s(s + 3 * c.snap_field_stride, r, tzz);
+        st2s(s + 4 * c.snap_field_stride, r, txz);
+      }
+      if (MODE == MODE_ACCUMULATE) {
+        if (own && j >= c.wx0 && j < c.wx1 && z0 + 1 >= c.wz0 && z0 < c.wz1) {
+          const double *s = m.snap + c.snap_offset;
+          const double2 fvx = ld2s(s, r), fvz = ld2s(s + c.snap_field_stride, r),
+                        fxx = ld2s(s + 2 * c.snap_field_stride, r),
+                        fzz = ld2s(s + 3 * c.snap_field_stride, r),
+                        fxz = ld2s(s + 4 * c.snap_field_stride, r);
+          double2 kr = *(reinterpret_cast<const double2 *>(m.k_rho) + r),
+                  kl = *(reinterpret_cast<const double2 *>(m.k_lam) + r),
+                  km = *(reinterpret_cast<const double2 *>(m.k_mu) + r);
+          if (z0 >= c.wz0 && z0 < c.wz1)
+            kernel_accumulate<M>(c.sidt, lm.x, mu.x, fvx.x, fvz.x, fxx.x, fzz.x, fxz.x, vx_0.x, vz_0.x,
+                                 txx.x, tzz.x, txz.x, kr.x, kl.x, km.x);
+          if (z0 + 1 >= c.wz0 && z0 + 1 < c.wz1)
+            kernel_accumulate<M>(c.sidt, lm.y, mu.y, fvx.y, fvz.y, fxx.y, fzz.y, fxz.y, vx_0.y, vz_0.y,
+                                 txx.y, tzz.y, txz.y, kr.y, kl.y, km.y);
+          st2s(m.k_rho, r, kr);
+          st2s(m.k_lam, r, kl);
+          st2s(m.k_mu, r, km);
+        }
+      }
+      // receiver sampling from the old velocities (src/fdModel.cpp:576-596)
+      if (c.point_mode == POINT_FORWARD && strip_rec) {
+        const int q1 = c.rec_row_start[j + 1];
+        for (int q = c.rec_row_start[j]; q < q1; ++q) {
+          const int z = c.rec_z[q];
+          if (own && (z >> 1) == kp) {
+            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
+            const double sx = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vx_0.y : vx_0.x), c.dxdz);
+            const double sz = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vz_0.y : vz_0.x), c.dxdz);
+            if (c.it == 0) {
+              m.ux[t] = sx;
+              m.uz[t] = sz;
+            } else {
+              m.ux[t] = __dadd_rn(m.ux[t - 1], sx);
+              m.uz[t] = __dadd_rn(m.uz[t - 1], sz);
+            }
+          }
+        }
+      }
+    }
+
+    // ---- stress update of row j (all lanes: halo lanes feed their neighbours) ----
+    if (j >= 2 && j < nx - 2) {
+      const double vxL_y = shfl_up1(vx_0.y), vxR_x = shfl_dn1(vx_0.x), vxR_y = shfl_dn1(vx_0.y);
+      const double vzL_x = shfl_up1(vz_0.x), vzL_y = shfl_up1(vz_0.y), vzR_x = shfl_dn1(vz_0.x);
+      if (za) {  // point (j, z0)
+        const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
+        const double dzm_vz = diff4<M>(c.k, vz_0.x, vzL_y, vzL_x, vz_0.y);
+        const double dzp_vx = diff4<M>(c.k, vx_0.y, vx_0.x, vxL_y, vxR_x);
+        const double dxm_vz = diff4<M>(c.k, vz_0.x, vz_m1.x, vz_m2.x, vz_p1.x);
+        const double tp = taper_at(c.taper_table, c.g.np, j, z0, nx, nz);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x, tp, txx.x, tzz.x, txz.x);
+      }
+      if (zb) {  // point (j, z0+1)
+        const double dxp_vx = diff4<M>(c.k, vx_p1.y, vx_0.y, vx_m1.y, vx_p2.y);
+        const double dzm_vz = diff4<M>(c.k, vz_0.y, vz_0.x, vzL_y, vzR_x);
+        const double dzp_vx = diff4<M>(c.k, vxR_x, vx_0.y, vx_0.x, vxR_y);
+        const double dxm_vz = diff4<M>(c.k, vz_0.y, vz_m1.y, vz_m2.y, vz_p1.y);
+        const double tp = taper_at(c.taper_table, c.g.np, j, z0 + 1, nx, nz);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y, tp, txx.y, tzz.y, txz.y);
+      }
+    }
+    if (row_mine && own) {
+      st2s(nxx, r, txx);
+      st2s(nzz, r, tzz);
+      st2s(nxz, r, txz);
+    }
+
+    // ---- velocity update of row x = j-2 (new stresses: txx x-2..x+1, txz x-1..x+2, tzz x) ----
+    const int x = j - 2;
+    if (x >= xs) {
+      const long long rv = r - 2 * ld2n;
+      const double2 b = d.b;
+      double2 vx = vx_m2, vz = vz_m2;
+      if (x >= 2 && x < nx - 2) {
+        const double xzL_x = shfl_up1(xz_m2.x), xzL_y = shfl_up1(xz_m2.y), xzR_x = shfl_dn1(xz_m2.x);
+        const double zzL_y = shfl_up1(zz_m2.y), zzR_x = shfl_dn1(zz_m2.x), zzR_y = shfl_dn1(zz_m2.y);
+        if (za) {
+          const double dxm_txx = diff4<M>(c.k, xx_m2.x, xx_m3.x, xx_m4.x, xx_m1.x);
+          const double dzm_txz = diff4<M>(c.k, xz_m2.x, xzL_y, xzL_x, xz_m2.y);
+          const double dxp_txz = diff4<M>(c.k, xz_m1.x, xz_m2.x, xz_m3.x, txz.x);
+          const double dzp_tzz = diff4<M>(c.k, zz_m2.y, zz_m2.x, zzL_y, zzR_x);
+          const double tp = taper_at(c.taper_table, c.g.np, x, z0, nx, nz);
+          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, tp, vx.x, vz.x);
+        }
+        if (zb) {
+          const double dxm_txx = diff4<M>(c.k, xx_m2.y, xx_m3.y, xx_m4.y, xx_m1.y);
+          const double dzm_txz = diff4<M>(c.k, xz_m2.y, xz_m2.x, xzL_y, xzR_x);
+          const double dxp_txz = diff4<M>(c.k, xz_m1.y, xz_m2.y, xz_m3.y, txz.y);
+          const double dzp_tzz = diff4<M>(c.k, zzR_x, zz_m2.y, zz_m2.x, zzR_y);
+          const double tp = taper_at(c.taper_table, c.g.np, x, z0 + 1, nx, nz);
+          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, tp, vx.y, vz.y);
+        }
+      }
+      // moment-tensor injection on the updated velocities (src/fdModel.cpp:681-751)
+      if (strip_ops) {
+        const int q1 = c.op_row_start[x + 1];
+        for (int q = c.op_row_start[x]; q < q1; ++q) {
+          const RowOp op = c.ops[q];
+          if (own && (op.z >> 1) == kp) {
+            const double w = c.stf[(size_t)op.source * c.nt + c.it];
+            const double bb = (op.z & 1) ? b.y : b.x;
+            const double amp = __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(op.weight, w), c.dt), bb), op.d4);
+            const bool odd = op.z & 1;
+            double t = op.field == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
+            t = op.sign > 0 ? __dadd_rn(t, amp) : __dsub_rn(t, amp);
+            if (op.field == 0) {
+              if (odd) vx.y = t; else vx.x = t;
+            } else {
+              if (odd) vz.y = t; else vz.x = t;
+            }
+          }
+        }
+      }
+      // adjoint-source injection at the receivers (src/fdModel.cpp:951-958)
+      if (c.point_mode == POINT_ADJOINT && strip_rec) {
+        const int q1 = c.rec_row_start[x + 1];
+        for (int q = c.rec_row_start[x]; q < q1; ++q) {
+          const int z = c.rec_z[q];
+          if (own && (z >> 1) == kp) {
+            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
+            const double bb = (z & 1) ? b.y : b.x;
+            const double ax = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.ax[t]), c.dxdz);
+            const double az = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.az[t]), c.dxdz);
+            if (z & 1) {
+              vx.y = __dadd_rn(vx.y, ax);
+              vz.y = __dadd_rn(vz.y, az);
+            } else {
+              vx.x = __dadd_rn(vx.x, ax);
+              vz.x = __dadd_rn(vz.x, az);
+            }
+          }
+        }
+      }
+      if (own) {
+        st2s(nvx, rv, vx);
+        st2s(nvz, rv, vz);
+      }
+    }
+
+    // rotate the windows
+    vx_m2 = vx_m1; vx_m1 = vx_0; vx_0 = vx_p1; vx_p1 = vx_p2;
+    vz_m2 = vz_m1; vz_m1 = vz_0; vz_0 = vz_p1;
+    xx_m4 = xx_m3; xx_m3 = xx_m2; xx_m2 = xx_m1; xx_m1 = txx;
+    xz_m3 = xz_m2; xz_m2 = xz_m1; xz_m1 = txz;
+    zz_m2 = zz_m1; zz_m1 = tzz;
+  }
+}
+
+template <class M, int MODE>
+__global__ void __launch_bounds__(128) fused_step_kernel(const FusedCommon c,
+                                                         const FusedModel *__restrict__ models) {
+  const int lane = threadIdx.x & 31;
+  const int zw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (zw >= c.n_zwarps) return;  // warp-uniform
+  const FusedModel &m = models[blockIdx.z];
+  const int kp = zw * kFusedOwnedPairs - 2 + lane;  // my z-pair (may lie outside the row: halo lanes)
+  const int xs = blockIdx.y * c.strip;
+  const int xe = min(xs + c.strip, c.g.nx);
+  GlobalRows rows{m.f[c.parity][0], m.f[c.parity][1], m.f[c.parity][2], m.f[c.parity][3], m.f[c.parity][4],
+                  m.lm, m.mu, m.b, (long long)(c.g.ld >> 1)};
+  fused_march<M, MODE>(c, m, rows, lane, kp, xs, xe);
+}
+
+// ------------------------------------------------------------------------------------------
+// Variant 3: the same march fed by a TMA pipeline.
+// A CTA = NW consumer warps (adjacent z-warps of one strip) + one producer warp.  For every
+// row of the march the producer's elected lane issues 8 bulk-asynchronous copies
+// (cp.async.bulk global -> shared, one contiguous row segment of NW*28+4 pairs per array)
+// into a ring of kPipeStages row slots, each guarded by a full/empty mbarrier pair.  The
+// copies run up to kPipeStages rows ahead of the consumers, so the bytes in flight per SM are
+// set by the ring depth (~100 KB per CTA), not by registers x occupancy as in variant 2.
+// Consumers wait on the row's `full` barrier, lift their 8 double2 out of shared memory,
+// release the slot at once (`empty` arrive, one lane per warp) and run the identical
+// arithmetic.  Results go straight from registers to global memory (coalesced 16 B / lane).
+// ------------------------------------------------------------------------------------------
+constexpr int kPipeArrays = 8;
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "PSV_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra PSV_DONE;\n"
+      "bra PSV_WAIT;\n"
+      "PSV_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+template <int NW>
+struct PipeGeom {
+  static constexpr int kOwned = NW * kFusedOwnedPairs;  // pairs owned by the CTA
+  static constexpr int kPairs = kOwned + 4;             // + 2 halo pairs on each side
+  static constexpr int kSeg = kPairs * 16;              // bytes of one row segment of one array
+  static constexpr int kStage = kSeg * kPipeArrays;     // bytes of one ring slot
+};
+
+// Row source of variant 3: the ring in shared memory.
+struct PipeRows {
+  const unsigned char *ring;  // first slot
+  unsigned full0, empty0;     // shared addresses of the barrier arrays
+  int stages, seg, stage_bytes;
+  int lane_off;               // byte offset of my pair inside a segment
+  int slot;
+  unsigned phase;
+  int lane;
+  __device__ __forceinline__ void fetch(long long, RowData &d) {
+    mbar_wait(full0 + 8 * slot, phase);
+    const unsigned char *s = ring + (size_t)slot * stage_bytes + lane_off;
+    d.vx_p2 = *reinterpret_cast<const double2 *>(s);
+    d.vz_p1 = *reinterpret_cast<const double2 *>(s + seg);
+    d.txx = *reinterpret_cast<const double2 *>(s + 2 * seg);
+    d.tzz = *reinterpret_cast<const double2 *>(s + 3 * seg);
+    d.txz = *reinterpret_cast<const double2 *>(s + 4 * seg);
+    d.lm = *reinterpret_cast<const double2 *>(s + 5 * seg);
+    d.mu = *reinterpret_cast<const double2 *>(s + 6 * seg);
+    d.b = *reinterpret_cast<const double2 *>(s + 7 * seg);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+    if (++slot == stages) {
+      slot = 0;
+      phase ^= 1;
+    }
+  }
+};
+
+template <class M, int MODE, int NW>
+__global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCommon c,
+                                                                   const FusedModel *__restrict__ models,
+                                                                   const int stages) {
+  using G = PipeGeom<NW>;
+  extern __shared__ __align__(128) unsigned char psv_smem[];
+  unsigned long long *bars = reinterpret_cast<unsigned long long *>(psv_smem);  // [stages] full, [stages] empty
+  unsigned char *ring = psv_smem + 128 * ((2 * stages * 8 + 127) / 128);
+  const unsigned full0 = smem_u32(bars), empty0 = full0 + 8 * stages;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, NW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const FusedModel &m = models[blockIdx.z];
+  const long long ld2n = c.g.ld >> 1;
+  const int xs = blockIdx.y * c.strip;
+  const int xe = min(xs + c.strip, c.g.nx);
+  const int kp_tile = blockIdx.x * G::kOwned - 2;  // first pair of the CTA's row segment
+
+  if (warp == NW) {
+    // ---- producer: one lane streams the rows of the strip into the ring ----
+    if (lane == 0) {
+      const double *src[kPipeArrays] = {m.f[c.parity][0], m.f[c.parity][1], m.f[c.parity][2], m.f[c.parity][3],
+                                        m.f[c.parity][4], m.lm,           m.mu,             m.b};
+      const long long row_off[kPipeArrays] = {2, 1, 0, 0, 0, 0, 0, -2};  // row of each array relative to j
+      int slot = 0;
+      unsigned phase = 0;
+      const unsigned ring_u32 = smem_u32(ring);
+      for (int j = xs - 2; j < xe + 2; ++j) {
+        mbar_wait(empty0 + 8 * slot, phase ^ 1);
+        const unsigned bar = full0 + 8 * slot;
+        mbar_expect_tx(bar, G::kStage);
+        const unsigned dst = ring_u32 + slot * G::kStage;
+#pragma unroll
+        for (int a = 0; a < kPipeArrays; ++a)
+          bulk_g2s(dst + a * G::kSeg,
+                   reinterpret_cast<const double2 *>(src[a]) + ((long long)j + row_off[a]) * ld2n + kp_tile,
+                   G::kSeg, bar);
+        if (++slot == stages) {
+          slot = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- consumers ----
+  PipeRows rows{ring, full0, empty0, stages, G::kSeg, G::kStage, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane};
+  const int kp = kp_tile + warp * kFusedOwnedPairs + lane;
+  fused_march<M, MODE>(c, m, rows, lane, kp, xs, xe);
+}
+
+}  // namespace psv

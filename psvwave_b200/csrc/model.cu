@@ -10,6 +10,7 @@
 #include <limits>
 #include <sstream>
 
+#include "fused.cuh"
 #include "kernels.cuh"
 #include "pointwise.cuh"
 
@@ -89,12 +90,13 @@ void Model::allocate() {
   const Config &c = cfg_;
   ld_ = round_up(c.nz, 16);
   grid_elems_ = (size_t)c.nx * ld_;
-  guard_ = 2 * (size_t)ld_ + 16;
+  guard_ = 6 * (size_t)ld_ + 512;  // fused.cuh reads rows -4..nx+3 and up to 30 pairs past a row end
   n_snap_alloc_ = (c.nt + c.snapshot_interval - 1) / c.snapshot_interval;
 
-  GridArray *grids[] = {&vx_, &vz_, &txx_, &tzz_, &txz_, &vp_, &vs_, &rho_, &lm_, &mu_, &b_,
-                        &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  GridArray *grids[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (GridArray *g : grids) *g = make_grid();
+  for (auto &set : fld_)
+    for (GridArray &g : set) g = make_grid();
   lame_kernels_.allocate(3 * grid_elems_ * sizeof(double));
   taper_table_.allocate((c.np_boundary + 1) * sizeof(double));
   stf_.allocate((size_t)c.n_sources * c.nt * sizeof(double));
@@ -173,6 +175,27 @@ void Model::build_plans() {
   copy_sync(rec_next_.as<int>(), next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice);
   copy_sync(rec_heads_.as<int>(), heads.data(), heads.size() * sizeof(int), cudaMemcpyHostToDevice);
 
+  // receivers bucketed by grid row for the fused step kernel: stable sort by ix keeps the
+  // receiver order inside a row (adjoint injection at coinciding receivers is order-sensitive)
+  {
+    std::vector<int> order(c.nr), row_start(c.nx + 1, 0), rz(std::max(c.nr, 1), 0), rid(std::max(c.nr, 1), 0);
+    for (int r = 0; r < c.nr; ++r) order[r] = r;
+    std::stable_sort(order.begin(), order.end(),
+                     [&](int a, int b) { return c.ix_receivers[a] < c.ix_receivers[b]; });
+    for (int r = 0; r < c.nr; ++r) ++row_start[c.ix_receivers[r] + 1];
+    for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
+    for (int q = 0; q < c.nr; ++q) {
+      rz[q] = c.iz_receivers[order[q]];
+      rid[q] = order[q];
+    }
+    rec_row_start_.allocate(row_start.size() * sizeof(int));
+    rec_row_z_.allocate(rz.size() * sizeof(int));
+    rec_row_id_.allocate(rid.size() * sizeof(int));
+    copy_sync(rec_row_start_.as<int>(), row_start.data(), row_start.size() * sizeof(int), cudaMemcpyHostToDevice);
+    copy_sync(rec_row_z_.as<int>(), rz.data(), rz.size() * sizeof(int), cudaMemcpyHostToDevice);
+    copy_sync(rec_row_id_.as<int>(), rid.data(), rid.size() * sizeof(int), cudaMemcpyHostToDevice);
+  }
+
   // sources: the 12 point updates per source in the order of src/fdModel.cpp:702-750
   const double dx4 = c.dx * c.dx * c.dx * c.dx, dz4 = c.dz * c.dz * c.dz * c.dz;
   for (int shot = 0; shot < c.n_shots; ++shot) {
@@ -214,6 +237,23 @@ void Model::build_plans() {
     }
     ShotPlan &p = plans_[shot];
     p.n_heads = (int)op_heads.size();
+    {  // the same operations bucketed by target row (stable: original order kept inside a row)
+      std::vector<int> order(ops.size()), row_start(c.nx + 1, 0);
+      for (size_t i = 0; i < ops.size(); ++i) order[i] = (int)i;
+      auto row_of = [&](int i) { return ops[i].point / ld_; };
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return row_of(a) < row_of(b); });
+      std::vector<RowOp> rops(std::max<size_t>(ops.size(), 1));
+      for (size_t q = 0; q < ops.size(); ++q) {
+        const InjectOp &o = ops[order[q]];
+        ++row_start[row_of(order[q]) + 1];
+        rops[q] = RowOp{o.point % ld_, o.field, o.source, 0, o.weight, o.sign, o.d4};
+      }
+      for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
+      p.row_ops.allocate(rops.size() * sizeof(RowOp));
+      p.op_row_start.allocate(row_start.size() * sizeof(int));
+      copy_sync(p.row_ops.as<RowOp>(), rops.data(), rops.size() * sizeof(RowOp), cudaMemcpyHostToDevice);
+      copy_sync(p.op_row_start.as<int>(), row_start.data(), row_start.size() * sizeof(int), cudaMemcpyHostToDevice);
+    }
     if (ops.empty()) continue;
     p.ops.allocate(ops.size() * sizeof(InjectOp));
     p.heads.allocate(op_heads.size() * sizeof(int));
@@ -241,17 +281,23 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   profile_ = o.profile_;
   strip_ = o.strip_;
   block_ = o.block_;
+  fused_strip_ = o.fused_strip_;
+  fused_block_ = o.fused_block_;
+  pipe_stages_ = o.pipe_stages_;
+  pipe_warps_ = o.pipe_warps_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
     if (src.empty()) return;
     if (dst.bytes() != src.bytes()) dst.allocate(src.bytes());
     copy_sync(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice);
   };
-  const GridArray *gs[] = {&o.vx_, &o.vz_, &o.txx_, &o.tzz_, &o.txz_, &o.vp_, &o.vs_, &o.rho_, &o.lm_,
-                           &o.mu_, &o.b_, &o.vp_kernel_, &o.vs_kernel_, &o.density_v_kernel_};
-  GridArray *gd[] = {&vx_, &vz_, &txx_, &tzz_, &txz_, &vp_, &vs_, &rho_, &lm_,
-                     &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  const GridArray *gs[] = {&o.vp_, &o.vs_, &o.rho_, &o.lm_, &o.mu_, &o.b_, &o.vp_kernel_, &o.vs_kernel_,
+                           &o.density_v_kernel_};
+  GridArray *gd[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (size_t i = 0; i < sizeof(gs) / sizeof(gs[0]); ++i) dcopy(gs[i]->buf, gd[i]->buf);
+  cur_ = o.cur_;
+  for (int p = 0; p < 2; ++p)
+    for (int k = 0; k < 5; ++k) dcopy(o.fld_[p][k].buf, fld_[p][k].buf);
   dcopy(o.lame_kernels_, lame_kernels_);
   dcopy(o.taper_table_, taper_table_);
   dcopy(o.stf_, stf_);
@@ -315,8 +361,9 @@ void Model::check_shot(int i_shot) const {
 }
 
 void Model::zero_dynamic_fields() {
-  GridArray *f[] = {&vx_, &vz_, &txx_, &tzz_, &txz_};
-  for (GridArray *g : f) PSV_CUDA(cudaMemsetAsync(g->buf.as<char>(), 0, g->buf.bytes(), stream_));
+  for (auto &set : fld_)
+    for (GridArray &g : set) PSV_CUDA(cudaMemsetAsync(g.buf.as<char>(), 0, g.buf.bytes(), stream_));
+  cur_ = 0;
 }
 
 void Model::ensure_snapshots(int i_shot) {
@@ -404,11 +451,11 @@ void Model::launch_stress(double sdt, int mode, int i_shot, int snap) {
   StressArgs a{};
   a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
   a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
-  a.vx = vx_.data();
-  a.vz = vz_.data();
-  a.txx = txx_.data();
-  a.tzz = tzz_.data();
-  a.txz = txz_.data();
+  a.vx = F(0);
+  a.vz = F(1);
+  a.txx = F(2);
+  a.tzz = F(3);
+  a.txz = F(4);
   a.lm = lm_.data();
   a.mu = mu_.data();
   a.taper_table = taper_table_.as<>();
@@ -440,16 +487,185 @@ void Model::launch_velocity(double sdt) {
   VelocityArgs a{};
   a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
   a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
-  a.txx = txx_.data();
-  a.tzz = tzz_.data();
-  a.txz = txz_.data();
-  a.vx = vx_.data();
-  a.vz = vz_.data();
+  a.txx = F(2);
+  a.tzz = F(3);
+  a.txz = F(4);
+  a.vx = F(0);
+  a.vz = F(1);
   a.b = b_.data();
   a.taper_table = taper_table_.as<>();
   a.strip = strip_;
   if (exact_) launch_velocity_t<ExactMath>(variant_, a, block_, stream_);
   else launch_velocity_t<FastMath>(variant_, a, block_, stream_);
+  ++stat_launches_;
+}
+
+// ---- variant 2: one fused launch per time step ------------------------------------------------
+void Model::fused_begin(int i_shot, int point_mode) {
+  const Config &c = cfg_;
+  FusedModel fm{};
+  for (int p = 0; p < 2; ++p)
+    for (int k = 0; k < 5; ++k) fm.f[p][k] = fld_[p][k].data();
+  fm.lm = lm_.data();
+  fm.mu = mu_.data();
+  fm.b = b_.data();
+  fm.snap = snapshots_[i_shot].empty() ? nullptr : snapshots_[i_shot].as<double>();
+  fm.k_lam = lame_kernels_.as<double>();
+  fm.k_mu = lame_kernels_.as<double>() + grid_elems_;
+  fm.k_rho = lame_kernels_.as<double>() + 2 * grid_elems_;
+  const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
+  fm.ux = rtf_ux_.as<>() + shot_rows;
+  fm.uz = rtf_uz_.as<>() + shot_rows;
+  fm.ax = a_stf_ux_.as<>() + shot_rows;
+  fm.az = a_stf_uz_.as<>() + shot_rows;
+  (void)point_mode;
+  if (fused_model_.empty()) fused_model_.allocate(sizeof(FusedModel));
+  // stream-ordered upload from a stack object: wait for it before the object dies
+  copy_sync(fused_model_.as<FusedModel>(), &fm, sizeof(FusedModel), cudaMemcpyHostToDevice);
+}
+
+namespace {
+template <class M>
+void launch_fused_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int block,
+                    cudaStream_t st) {
+  if (mode == MODE_SNAPSHOT) fused_step_kernel<M, MODE_SNAPSHOT><<<grid, block, 0, st>>>(fc, models);
+  else if (mode == MODE_ACCUMULATE) fused_step_kernel<M, MODE_ACCUMULATE><<<grid, block, 0, st>>>(fc, models);
+  else fused_step_kernel<M, MODE_PLAIN><<<grid, block, 0, st>>>(fc, models);
+}
+}  // namespace
+
+// Rows per warp such that the launch is a whole number of waves of resident blocks (the warps
+// of a launch run in lock-step through their strips, so a partial last wave costs a full one).
+int Model::fused_auto_strip(int n_zwarps, int batch) {
+  if (fused_resident_blocks_ == 0) {
+    int per_sm = 0, sms = 0;
+    PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_step_kernel<FastMath, MODE_PLAIN>,
+                                                           fused_block_, 0));
+    PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+    fused_resident_blocks_ = std::max(1, per_sm * sms);
+  }
+  const int wpb = fused_block_ / 32;
+  const int blocks_x = ((n_zwarps + wpb - 1) / wpb) * batch;
+  const int nx = cfg_.nx;
+  for (int waves = 1;; ++waves) {
+    const int n_strips = std::max(1, waves * fused_resident_blocks_ / blocks_x);
+    const int strip = (nx + n_strips - 1) / n_strips;
+    if (strip <= 96 || n_strips >= nx) return std::max(strip, 8);
+  }
+}
+
+namespace {
+template <class M, int MODE, int NW>
+void launch_pipe_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
+                   cudaStream_t st) {
+  static size_t configured = 0;  // per instantiation
+  if (configured < smem) {
+    PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<M, MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    configured = smem;
+  }
+  fused_pipe_kernel<M, MODE, NW><<<grid, (NW + 1) * 32, smem, st>>>(fc, models, stages);
+}
+template <class M, int NW>
+void launch_pipe_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
+                   cudaStream_t st) {
+  if (mode == MODE_SNAPSHOT) launch_pipe_k<M, MODE_SNAPSHOT, NW>(fc, models, grid, stages, smem, st);
+  else if (mode == MODE_ACCUMULATE) launch_pipe_k<M, MODE_ACCUMULATE, NW>(fc, models, grid, stages, smem, st);
+  else launch_pipe_k<M, MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
+}
+template <int NW>
+size_t pipe_smem_bytes(int stages) {
+  return 128 * ((2 * (size_t)stages * 8 + 127) / 128) + (size_t)stages * PipeGeom<NW>::kStage;
+}
+}  // namespace
+
+// Launch geometry of variant 3: CTAs per row, and rows per CTA such that the launch is a whole
+// number of waves of resident CTAs.
+void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
+  const int nw = pipe_warps_;
+  const int owned = nw * kFusedOwnedPairs;
+  *tiles = (ld_ / 2 + owned - 1) / owned;
+  *smem = nw == 8 ? pipe_smem_bytes<8>(pipe_stages_) : pipe_smem_bytes<4>(pipe_stages_);
+  if (pipe_resident_ == 0) {
+    int per_sm = 0, sms = 0;
+    if (nw == 8) {
+      PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, 8>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
+      PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, 8>,
+                                                             (nw + 1) * 32, *smem));
+    } else {
+      PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, 4>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
+      PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, 4>,
+                                                             (nw + 1) * 32, *smem));
+    }
+    PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+    pipe_resident_ = std::max(1, per_sm * sms);
+  }
+  if (fused_strip_ > 0) {
+    *strip = fused_strip_;
+    return;
+  }
+  const int blocks_x = *tiles * batch;
+  const int nx = cfg_.nx;
+  for (int waves = 1;; ++waves) {
+    const int n_strips = std::max(1, waves * pipe_resident_ / blocks_x);
+    const int st = (nx + n_strips - 1) / n_strips;
+    if (st <= 128 || n_strips >= nx) {
+      *strip = std::max(st, 8);
+      return;
+    }
+  }
+}
+
+void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it) {
+  const Config &c = cfg_;
+  FusedCommon fc{};
+  fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
+  fc.taper_table = taper_table_.as<>();
+  fc.parity = cur_;
+  fc.n_zwarps = (ld_ / 2 + kFusedOwnedPairs - 1) / kFusedOwnedPairs;
+  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ == 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1));
+  fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
+  fc.snap_offset = (size_t)snap * grid_elems_;
+  fc.wx0 = c.np_boundary + c.nx_inner_boundary;
+  fc.wx1 = c.np_boundary + c.nx_inner - c.nx_inner_boundary;
+  fc.wz0 = c.np_boundary + c.nz_inner_boundary;
+  fc.wz1 = c.np_boundary + c.nz_inner - c.nz_inner_boundary;
+  fc.sidt = c.snapshot_interval * c.dt;
+  fc.point_mode = point_mode;
+  fc.nt = c.nt;
+  fc.it = it;
+  fc.dt = c.dt;
+  fc.dxdz = c.dx * c.dz;
+  fc.rec_row_start = rec_row_start_.as<int>();
+  fc.rec_z = rec_row_z_.as<int>();
+  fc.rec_id = rec_row_id_.as<int>();
+  fc.op_row_start = plans_[i_shot].op_row_start.as<int>();
+  fc.ops = plans_[i_shot].row_ops.as<RowOp>();
+  fc.stf = stf_.as<>();
+  const FusedModel *models = fused_model_.as<FusedModel>();
+  if (variant_ == 3) {
+    int tiles = 0, strip = 0;
+    size_t smem = 0;
+    pipe_geometry(1, &tiles, &strip, &smem);
+    fc.strip = strip;
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
+    if (pipe_warps_ == 8) {
+      if (exact_) launch_pipe_m<ExactMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      else launch_pipe_m<FastMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+    } else {
+      if (exact_) launch_pipe_m<ExactMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      else launch_pipe_m<FastMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+    }
+  } else {
+    const int wpb = fused_block_ / 32;
+    dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, 1);
+    if (exact_) launch_fused_m<ExactMath>(mode, fc, models, grid, fused_block_, stream_);
+    else launch_fused_m<FastMath>(mode, fc, models, grid, fused_block_, stream_);
+  }
+  cur_ ^= 1;
   ++stat_launches_;
 }
 
@@ -466,7 +682,19 @@ struct Profiler {  // CUDA events around sampled sweep launches
       for (cudaEvent_t &x : ev) PSV_CUDA(cudaEventCreate(&x));
     }
   }
-  bool sample(int it) const { return on && it % every == 0 && 3 * (n + 1) <= (int)ev.size(); }
+  int countdown = 0;
+  // every `every`-th step, skipping snapshot / correlation steps (`special`): the sampled mean is
+  // the plain sweep's duration
+  bool sample(bool special) {
+    if (!on || 3 * (n + 1) > (int)ev.size()) return false;
+    if (countdown > 0) {
+      --countdown;
+      return false;
+    }
+    if (special) return false;
+    countdown = every - 1;
+    return true;
+  }
   void mark(int k) { PSV_CUDA(cudaEventRecord(ev[3 * n + k], st)); }
   void next() { ++n; }
   void collect(double &stress_ms, double &velocity_ms) {
@@ -498,20 +726,40 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   Profiler prof(prof_events_, stream_, profile_, c.nt);
 
   const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
-  RecordArgs ra{vx_.data(), vz_.data(), rec_index_.as<int>(), rtf_ux_.as<>() + shot_rows,
+  RecordArgs ra{F(0), F(1), rec_index_.as<int>(), rtf_ux_.as<>() + shot_rows,
                 rtf_uz_.as<>() + shot_rows, c.nr, c.nt, 0, c.dt, c.dx * c.dz};
   const ShotPlan &plan = plans_[i_shot];
-  InjectArgs ia{vx_.data(), vz_.data(), b_.data(), stf_.as<>(), plan.ops.as<InjectOp>(),
+  InjectArgs ia{F(0), F(1), b_.data(), stf_.as<>(), plan.ops.as<InjectOp>(),
                 plan.heads.as<int>(), plan.n_heads, c.nt, 0, c.dt};
 
+  if (variant_ >= 2) fused_begin(i_shot, POINT_FORWARD);
   for (int it = 0; it < c.nt; ++it) {
+    if (variant_ >= 2) {
+      const bool snap = store_fields && it % c.snapshot_interval == 0;
+      const bool sample = prof.sample(snap);
+      if (sample) prof.mark(0);
+      launch_fused(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, POINT_FORWARD, i_shot, it / c.snapshot_interval, it);
+      if (sample) {
+        prof.mark(1);
+        prof.mark(2);
+        prof.next();
+      }
+      if (output_wavefields && it % 10 == 0) write_wavefield_files(it);
+      continue;
+    }
+    // the point kernels take the state pointers per step (the fused variant may have left the
+    // current state in either buffer; variants 0/1 update it in place)
+    ra.vx = F(0);
+    ra.vz = F(1);
+    ia.vx = F(0);
+    ia.vz = F(1);
     if (c.nr > 0) {
       ra.it = it;
       record_receivers_kernel<<<blocks_for(c.nr, 128), 128, 0, stream_>>>(ra);
       ++stat_launches_;
     }
     const bool snap = store_fields && it % c.snapshot_interval == 0;
-    const bool sample = prof.sample(it);
+    const bool sample = prof.sample(snap);
     if (sample) prof.mark(0);
     launch_stress(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, i_shot, it / c.snapshot_interval);
     if (sample) prof.mark(1);
@@ -555,12 +803,24 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   Profiler prof(prof_events_, stream_, profile_, c.nt);
 
   const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
-  AdjointInjectArgs aa{vx_.data(), vz_.data(), b_.data(), a_stf_ux_.as<>() + shot_rows,
+  AdjointInjectArgs aa{F(0), F(1), b_.data(), a_stf_ux_.as<>() + shot_rows,
                        a_stf_uz_.as<>() + shot_rows, rec_index_.as<int>(), rec_next_.as<int>(),
                        rec_heads_.as<int>(), n_rec_heads_, c.nt, 0, c.dt, c.dx * c.dz};
+  if (variant_ >= 2) fused_begin(i_shot, POINT_ADJOINT);
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
-    const bool sample = prof.sample(it);
+    const bool sample = prof.sample(corr);
+    if (variant_ >= 2) {
+      if (sample) prof.mark(0);
+      launch_fused(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, c.nr > 0 ? POINT_ADJOINT : POINT_NONE, i_shot,
+                   it / c.snapshot_interval, it);
+      if (sample) {
+        prof.mark(1);
+        prof.mark(2);
+        prof.next();
+      }
+      continue;
+    }
     if (sample) prof.mark(0);
     launch_stress(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, i_shot, it / c.snapshot_interval);
     if (sample) prof.mark(1);
@@ -743,11 +1003,11 @@ void Model::get_array(psv_array which, double *out, size_t count) {
   const size_t grid = (size_t)c.nx * c.nz;
   double *k = lame_kernels_.as<double>();
   switch (which) {
-    case PSV_VX: return grid_to_host(vx_.data(), out);
-    case PSV_VZ: return grid_to_host(vz_.data(), out);
-    case PSV_TXX: return grid_to_host(txx_.data(), out);
-    case PSV_TZZ: return grid_to_host(tzz_.data(), out);
-    case PSV_TXZ: return grid_to_host(txz_.data(), out);
+    case PSV_VX: return grid_to_host(F(0), out);
+    case PSV_VZ: return grid_to_host(F(1), out);
+    case PSV_TXX: return grid_to_host(F(2), out);
+    case PSV_TZZ: return grid_to_host(F(3), out);
+    case PSV_TXZ: return grid_to_host(F(4), out);
     case PSV_LM: return grid_to_host(lm_.data(), out);
     case PSV_MU: return grid_to_host(mu_.data(), out);
     case PSV_B_VX:
@@ -1043,6 +1303,21 @@ void Model::set_option(const std::string &name, long long v) {
   } else if (name == "strip") {
     if (v < 1) throw invalid_argument("strip must be >= 1");
     strip_ = (int)v;
+  } else if (name == "fused_strip") {
+    if (v < 0) throw invalid_argument("fused_strip must be >= 0 (0 = whole waves)");
+    fused_strip_ = (int)v;
+  } else if (name == "pipe_stages") {
+    if (v < 2 || v > 16) throw invalid_argument("pipe_stages must be in 2..16");
+    pipe_stages_ = (int)v;
+    pipe_resident_ = 0;
+  } else if (name == "pipe_warps") {
+    if (v != 4 && v != 8) throw invalid_argument("pipe_warps must be 4 or 8");
+    pipe_warps_ = (int)v;
+    pipe_resident_ = 0;
+  } else if (name == "fused_block") {
+    if (v != 32 && v != 64 && v != 128) throw invalid_argument("fused_block must be 32, 64 or 128");
+    fused_block_ = (int)v;
+    fused_resident_blocks_ = 0;
   } else if (name == "block") {
     if (v != 32 && v != 64 && v != 96 && v != 128) throw invalid_argument("block must be 32, 64, 96 or 128");
     block_ = (int)v;
@@ -1057,6 +1332,10 @@ long long Model::get_option(const std::string &name) const {
   if (name == "profile") return profile_;
   if (name == "strip") return strip_;
   if (name == "block") return block_;
+  if (name == "fused_strip") return fused_strip_;
+  if (name == "fused_block") return fused_block_;
+  if (name == "pipe_stages") return pipe_stages_;
+  if (name == "pipe_warps") return pipe_warps_;
   throw invalid_argument("Unknown option '" + name + "'.");
 }
 

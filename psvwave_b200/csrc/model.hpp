@@ -67,7 +67,7 @@ struct GridArray {
 
 class Model {
  public:
-  static constexpr int kVariantCount = 2;
+  static constexpr int kVariantCount = 4;
   explicit Model(Config cfg, int device);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -119,6 +119,7 @@ class Model {
   struct ShotPlan {  // per-shot device lists for the point operations
     DeviceBuffer ops, heads;
     int n_heads = 0;
+    DeviceBuffer row_ops, op_row_start;  // the same operations bucketed by grid row (fused.cuh)
   };
 
   void allocate();
@@ -136,6 +137,12 @@ class Model {
   double misfit_of_range(size_t first, size_t count);
   void launch_stress(double sdt, int mode, int i_shot, int snap);
   void launch_velocity(double sdt);
+  // variant 2: one fused launch per time step (fused.cuh)
+  void fused_begin(int i_shot, int point_mode);
+  int fused_auto_strip(int n_zwarps, int batch);
+  void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
+  void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it);
+  double *F(int k) const { return fld_[cur_][k].data(); }  // current state: vx vz txx tzz txz
   void write_wavefield_files(int it);
 
   Config cfg_;
@@ -151,7 +158,8 @@ class Model {
   int n_snap_alloc_ = 0;  // ceil(nt / snapshot_interval)
 
   // grid arrays
-  GridArray vx_, vz_, txx_, tzz_, txz_;       // dynamic fields
+  GridArray fld_[2][5];                       // dynamic fields vx vz txx tzz txz, double-buffered
+  int cur_ = 0;                               // which buffer holds the current state
   GridArray vp_, vs_, rho_, lm_, mu_, b_;     // medium
   DeviceBuffer lame_kernels_;                 // [lambda | mu | density_l], each nx*ld
   GridArray vp_kernel_, vs_kernel_, density_v_kernel_;
@@ -164,6 +172,8 @@ class Model {
   DeviceBuffer rtf_ux_, rtf_uz_, obs_ux_, obs_uz_, a_stf_ux_, a_stf_uz_;  // [n_shots][nr][nt]
   DeviceBuffer rec_index_, rec_next_, rec_heads_;
   int n_rec_heads_ = 0;
+  DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_;  // receivers bucketed by grid row (fused.cuh)
+  DeviceBuffer fused_model_;                             // one FusedModel (device copy of the pointers)
   std::vector<ShotPlan> plans_;
   std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
   std::vector<DeviceBuffer> snapshot_pool_;  // released buffers, reused by ensure_snapshots
@@ -172,10 +182,13 @@ class Model {
   double misfit_ = 0.0;
 
   // options / statistics
-  int variant_ = 1;
+  int variant_ = 2;
   bool exact_ = false;
   bool profile_ = false;
   int strip_ = 16, block_ = 128;
+  int fused_strip_ = 0 /* 0 = whole waves */, fused_block_ = 128;
+  int fused_resident_blocks_ = 0;
+  int pipe_stages_ = 6, pipe_warps_ = 4, pipe_resident_ = 0;
   double stat_elapsed_ms_ = 0, stat_stress_ms_ = 0, stat_velocity_ms_ = 0;
   long long stat_launches_ = 0;
 };

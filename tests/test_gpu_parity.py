@@ -38,11 +38,13 @@ def close(a, b, what, exact):
 
 
 VARIANTS = [dict(variant=0, exact=1), dict(variant=0, exact=0), dict(variant=1, exact=1), dict(variant=1, exact=0),
-            dict(variant=2, exact=1), dict(variant=2, exact=0)]
+            dict(variant=2, exact=1), dict(variant=2, exact=0), dict(variant=3, exact=1), dict(variant=3, exact=0),
+            dict(variant=3, exact=1, pipe_warps=8, pipe_stages=3), dict(variant=2, exact=1, fused_strip=8)]
 
 
 def variant_id(o):
-    return f"v{o['variant']}-{'exact' if o['exact'] else 'fast'}"
+    extra = "".join(f"-{k}{v}" for k, v in o.items() if k not in ("variant", "exact"))
+    return f"v{o['variant']}-{'exact' if o['exact'] else 'fast'}{extra}"
 
 
 def supported(m_opts):
