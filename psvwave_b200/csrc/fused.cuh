@@ -66,6 +66,7 @@ struct FusedCommon {
   int parity;       // old state = f[parity], new state = f[parity ^ 1]
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
+  size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
   // snapshots / kernel accumulation
   size_t snap_field_stride;  // n_snap_alloc * nx*ld
   size_t snap_offset;        // snapshot index * nx*ld
@@ -90,6 +91,16 @@ __device__ __forceinline__ double2 ld2s(const double *p, long long pair) {
 }
 __device__ __forceinline__ void st2s(double *p, long long pair, double2 v) {
   *(reinterpret_cast<double2 *>(p) + pair) = v;
+}
+
+// min of two taper values (no NaNs here, so a compare-select is exact and cheaper than fmin)
+__device__ __forceinline__ double dmin2(double a, double b) { return a < b ? a : b; }
+// Taper table entry for distance-to-edge d (clamped into the table).  The table is monotone,
+// so taper(ix, iz) = min(table[row distance], table[column distance]) (src/fdModel.cpp:263-298).
+__device__ __forceinline__ double taper_axis(const double *__restrict__ table, int np, int i, int n) {
+  int d = min(i, n - 1 - i) + 1;
+  d = max(min(d, np), 0);
+  return __ldg(table + d);
 }
 
 // The 8 double2 a lane needs for one iteration of the march (row j; velocities of row j-2).
@@ -126,6 +137,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
   const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
   const bool za = z0 >= 2 && z0 < nz - 2;
   const bool zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
+  const double tza = taper_axis(c.taper_table, c.g.np, z0, nz), tzb = taper_axis(c.taper_table, c.g.np, z0 + 1, nz);
 
   const double *__restrict__ ovx = m.f[c.parity][0], *__restrict__ ovz = m.f[c.parity][1];
   double *__restrict__ nvx = m.f[c.parity ^ 1][0], *__restrict__ nvz = m.f[c.parity ^ 1][1];
@@ -160,6 +172,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
     double2 txx = d.txx, tzz = d.tzz, txz = d.txz;
     const double2 lm = d.lm, mu = d.mu;
     const bool row_mine = j >= xs && j < xe;  // warp-uniform
+    const double tr_j = taper_axis(c.taper_table, c.g.np, j, nx), tr_x = taper_axis(c.taper_table, c.g.np, j - 2, nx);
 
     if (row_mine) {
       if (MODE == MODE_SNAPSHOT && own) {
@@ -212,26 +225,34 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       }
     }
 
-    // ---- stress update of row j (all lanes: halo lanes feed their neighbours) ----
-    if (j >= 2 && j < nx - 2) {
+    // ---- stress update of row j (all lanes: halo lanes feed their neighbours; masked points
+    //      keep their value through selects, not branches) ----
+    {
       const double vxL_y = shfl_up1(vx_0.y), vxR_x = shfl_dn1(vx_0.x), vxR_y = shfl_dn1(vx_0.y);
       const double vzL_x = shfl_up1(vz_0.x), vzL_y = shfl_up1(vz_0.y), vzR_x = shfl_dn1(vz_0.x);
-      if (za) {  // point (j, z0)
+      const bool rowok = j >= 2 && j < nx - 2;
+      double axx = txx.x, azz = tzz.x, axz = txz.x, bxx = txx.y, bzz = tzz.y, bxz = txz.y;
+      {  // point (j, z0)
         const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
         const double dzm_vz = diff4<M>(c.k, vz_0.x, vzL_y, vzL_x, vz_0.y);
         const double dzp_vx = diff4<M>(c.k, vx_0.y, vx_0.x, vxL_y, vxR_x);
         const double dxm_vz = diff4<M>(c.k, vz_0.x, vz_m1.x, vz_m2.x, vz_p1.x);
-        const double tp = taper_at(c.taper_table, c.g.np, j, z0, nx, nz);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x, tp, txx.x, tzz.x, txz.x);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x, dmin2(tr_j, tza), axx, azz, axz);
       }
-      if (zb) {  // point (j, z0+1)
+      {  // point (j, z0+1)
         const double dxp_vx = diff4<M>(c.k, vx_p1.y, vx_0.y, vx_m1.y, vx_p2.y);
         const double dzm_vz = diff4<M>(c.k, vz_0.y, vz_0.x, vzL_y, vzR_x);
         const double dzp_vx = diff4<M>(c.k, vxR_x, vx_0.y, vx_0.x, vxR_y);
         const double dxm_vz = diff4<M>(c.k, vz_0.y, vz_m1.y, vz_m2.y, vz_p1.y);
-        const double tp = taper_at(c.taper_table, c.g.np, j, z0 + 1, nx, nz);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y, tp, txx.y, tzz.y, txz.y);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y, dmin2(tr_j, tzb), bxx, bzz, bxz);
       }
+      const bool ua = rowok && za, ub = rowok && zb;
+      txx.x = ua ? axx : txx.x;
+      tzz.x = ua ? azz : tzz.x;
+      txz.x = ua ? axz : txz.x;
+      txx.y = ub ? bxx : txx.y;
+      tzz.y = ub ? bzz : tzz.y;
+      txz.y = ub ? bxz : txz.y;
     }
     if (row_mine && own) {
       st2s(nxx, r, txx);
@@ -245,25 +266,30 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       const long long rv = r - 2 * ld2n;
       const double2 b = d.b;
       double2 vx = vx_m2, vz = vz_m2;
-      if (x >= 2 && x < nx - 2) {
+      {
         const double xzL_x = shfl_up1(xz_m2.x), xzL_y = shfl_up1(xz_m2.y), xzR_x = shfl_dn1(xz_m2.x);
         const double zzL_y = shfl_up1(zz_m2.y), zzR_x = shfl_dn1(zz_m2.x), zzR_y = shfl_dn1(zz_m2.y);
-        if (za) {
+        const bool rowok = x >= 2 && x < nx - 2;
+        double avx = vx.x, avz = vz.x, bvx = vx.y, bvz = vz.y;
+        {
           const double dxm_txx = diff4<M>(c.k, xx_m2.x, xx_m3.x, xx_m4.x, xx_m1.x);
           const double dzm_txz = diff4<M>(c.k, xz_m2.x, xzL_y, xzL_x, xz_m2.y);
           const double dxp_txz = diff4<M>(c.k, xz_m1.x, xz_m2.x, xz_m3.x, txz.x);
           const double dzp_tzz = diff4<M>(c.k, zz_m2.y, zz_m2.x, zzL_y, zzR_x);
-          const double tp = taper_at(c.taper_table, c.g.np, x, z0, nx, nz);
-          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, tp, vx.x, vz.x);
+          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, dmin2(tr_x, tza), avx, avz);
         }
-        if (zb) {
+        {
           const double dxm_txx = diff4<M>(c.k, xx_m2.y, xx_m3.y, xx_m4.y, xx_m1.y);
           const double dzm_txz = diff4<M>(c.k, xz_m2.y, xz_m2.x, xzL_y, xzR_x);
           const double dxp_txz = diff4<M>(c.k, xz_m1.y, xz_m2.y, xz_m3.y, txz.y);
           const double dzp_tzz = diff4<M>(c.k, zzR_x, zz_m2.y, zz_m2.x, zzR_y);
-          const double tp = taper_at(c.taper_table, c.g.np, x, z0 + 1, nx, nz);
-          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, tp, vx.y, vz.y);
+          velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, dmin2(tr_x, tzb), bvx, bvz);
         }
+        const bool ua = rowok && za, ub = rowok && zb;
+        vx.x = ua ? avx : vx.x;
+        vz.x = ua ? avz : vz.x;
+        vx.y = ub ? bvx : vx.y;
+        vz.y = ub ? bvz : vz.y;
       }
       // moment-tensor injection on the updated velocities (src/fdModel.cpp:681-751)
       if (strip_ops) {

@@ -13,6 +13,7 @@
 #include "fused.cuh"
 #include "kernels.cuh"
 #include "pointwise.cuh"
+#include "window.cuh"
 
 namespace psv {
 
@@ -90,13 +91,14 @@ void Model::allocate() {
   const Config &c = cfg_;
   ld_ = round_up(c.nz, 16);
   grid_elems_ = (size_t)c.nx * ld_;
-  guard_ = 6 * (size_t)ld_ + 512;  // fused.cuh reads rows -4..nx+3 and up to 30 pairs past a row end
+  guard_ = 6 * (size_t)ld_ + 1024;  // fused.cuh reads rows -4..nx+3 and up to 30 pairs past a row end
   n_snap_alloc_ = (c.nt + c.snapshot_interval - 1) / c.snapshot_interval;
 
   GridArray *grids[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (GridArray *g : grids) *g = make_grid();
-  for (auto &set : fld_)
-    for (GridArray &g : set) g = make_grid();
+  // the ten state arrays (2 buffers x vx vz txx tzz txz) sit in ONE allocation at a constant stride
+  field_stride_ = grid_elems_ + 2 * guard_;
+  fields_.allocate(10 * field_stride_ * sizeof(double));
   lame_kernels_.allocate(3 * grid_elems_ * sizeof(double));
   taper_table_.allocate((c.np_boundary + 1) * sizeof(double));
   stf_.allocate((size_t)c.n_sources * c.nt * sizeof(double));
@@ -284,6 +286,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   fused_strip_ = o.fused_strip_;
   fused_block_ = o.fused_block_;
   pipe_stages_ = o.pipe_stages_;
+  win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
@@ -296,8 +299,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   GridArray *gd[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (size_t i = 0; i < sizeof(gs) / sizeof(gs[0]); ++i) dcopy(gs[i]->buf, gd[i]->buf);
   cur_ = o.cur_;
-  for (int p = 0; p < 2; ++p)
-    for (int k = 0; k < 5; ++k) dcopy(o.fld_[p][k].buf, fld_[p][k].buf);
+  dcopy(o.fields_, fields_);
   dcopy(o.lame_kernels_, lame_kernels_);
   dcopy(o.taper_table_, taper_table_);
   dcopy(o.stf_, stf_);
@@ -361,8 +363,7 @@ void Model::check_shot(int i_shot) const {
 }
 
 void Model::zero_dynamic_fields() {
-  for (auto &set : fld_)
-    for (GridArray &g : set) PSV_CUDA(cudaMemsetAsync(g.buf.as<char>(), 0, g.buf.bytes(), stream_));
+  PSV_CUDA(cudaMemsetAsync(fields_.as<char>(), 0, fields_.bytes(), stream_));
   cur_ = 0;
 }
 
@@ -505,7 +506,7 @@ void Model::fused_begin(int i_shot, int point_mode) {
   const Config &c = cfg_;
   FusedModel fm{};
   for (int p = 0; p < 2; ++p)
-    for (int k = 0; k < 5; ++k) fm.f[p][k] = fld_[p][k].data();
+    for (int k = 0; k < 5; ++k) fm.f[p][k] = field_ptr(p, k);
   fm.lm = lm_.data();
   fm.mu = mu_.data();
   fm.b = b_.data();
@@ -579,6 +580,76 @@ size_t pipe_smem_bytes(int stages) {
 }
 }  // namespace
 
+// ---- variant 4: shared-memory window (window.cuh) ----------------------------------------------
+namespace {
+struct WinConfig {  // compiled (consumer warps, ring-T depth, min CTAs/SM) triples
+  int nw, st, minb;
+};
+constexpr WinConfig kWinConfigs[] = {{4, 2, 3}, {10, 2, 1}, {8, 2, 1}, {10, 4, 1}, {4, 4, 2}, {12, 2, 1}};
+constexpr int kWinConfigCount = sizeof(kWinConfigs) / sizeof(kWinConfigs[0]);
+
+template <class M, int MODE, int NW, int ST, int MINB>
+void launch_win_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream, int *occupancy) {
+  static bool configured = false;  // per instantiation
+  auto kern = window_step_kernel<M, MODE, NW, ST, MINB>;
+  constexpr int smem = WinLayout<NW, ST>::kTotal;
+  if (!configured) {
+    PSV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  if (occupancy) {
+    PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occupancy, kern, (NW + 1) * 32, smem));
+    return;
+  }
+  kern<<<grid, (NW + 1) * 32, smem, stream>>>(fc, models);
+}
+template <class M, int NW, int ST, int MINB>
+void launch_win_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream, int *occ) {
+  if (mode == MODE_SNAPSHOT) launch_win_k<M, MODE_SNAPSHOT, NW, ST, MINB>(fc, models, grid, stream, occ);
+  else if (mode == MODE_ACCUMULATE) launch_win_k<M, MODE_ACCUMULATE, NW, ST, MINB>(fc, models, grid, stream, occ);
+  else launch_win_k<M, MODE_PLAIN, NW, ST, MINB>(fc, models, grid, stream, occ);
+}
+template <class M>
+void launch_win(int cfg, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream,
+                int *occ) {
+  switch (cfg) {
+    case 0: return launch_win_m<M, 4, 2, 3>(mode, fc, models, grid, stream, occ);
+    case 1: return launch_win_m<M, 10, 2, 1>(mode, fc, models, grid, stream, occ);
+    case 2: return launch_win_m<M, 8, 2, 1>(mode, fc, models, grid, stream, occ);
+    case 3: return launch_win_m<M, 10, 4, 1>(mode, fc, models, grid, stream, occ);
+    case 4: return launch_win_m<M, 4, 4, 2>(mode, fc, models, grid, stream, occ);
+    default: return launch_win_m<M, 12, 2, 1>(mode, fc, models, grid, stream, occ);
+  }
+}
+}  // namespace
+
+void Model::win_geometry(int batch, int *tiles, int *strip) {
+  const int nw = kWinConfigs[win_config_].nw;
+  const int owned = nw * kWinOwned;
+  *tiles = (ld_ / 2 + owned - 1) / owned;
+  if (win_resident_ == 0) {
+    int per_sm = 0, sms = 0;
+    FusedCommon dummy{};
+    launch_win<FastMath>(win_config_, MODE_PLAIN, dummy, nullptr, dim3(1), stream_, &per_sm);
+    PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+    win_resident_ = std::max(1, per_sm * sms);
+  }
+  if (fused_strip_ > 0) {
+    *strip = fused_strip_;
+    return;
+  }
+  const int blocks_x = *tiles * batch;
+  const int nx = cfg_.nx;
+  for (int waves = 1;; ++waves) {
+    const int n_strips = std::max(1, waves * win_resident_ / blocks_x);
+    const int s = (nx + n_strips - 1) / n_strips;
+    if (s <= 128 || n_strips >= nx) {
+      *strip = std::max(s, 8);
+      return;
+    }
+  }
+}
+
 // Launch geometry of variant 3: CTAs per row, and rows per CTA such that the launch is a whole
 // number of waves of resident CTAs.
 void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
@@ -625,8 +696,9 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
   fc.taper_table = taper_table_.as<>();
   fc.parity = cur_;
+  fc.field_stride = field_stride_;
   fc.n_zwarps = (ld_ / 2 + kFusedOwnedPairs - 1) / kFusedOwnedPairs;
-  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ == 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1));
+  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1));
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
   fc.wx0 = c.np_boundary + c.nx_inner_boundary;
@@ -646,7 +718,14 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.ops = plans_[i_shot].row_ops.as<RowOp>();
   fc.stf = stf_.as<>();
   const FusedModel *models = fused_model_.as<FusedModel>();
-  if (variant_ == 3) {
+  if (variant_ == 4) {
+    int tiles = 0, strip = 0;
+    win_geometry(1, &tiles, &strip);
+    fc.strip = strip;
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
+    if (exact_) launch_win<ExactMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
+    else launch_win<FastMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
+  } else if (variant_ == 3) {
     int tiles = 0, strip = 0;
     size_t smem = 0;
     pipe_geometry(1, &tiles, &strip, &smem);
@@ -1306,6 +1385,10 @@ void Model::set_option(const std::string &name, long long v) {
   } else if (name == "fused_strip") {
     if (v < 0) throw invalid_argument("fused_strip must be >= 0 (0 = whole waves)");
     fused_strip_ = (int)v;
+  } else if (name == "win_config") {
+    if (v < 0 || v >= kWinConfigCount) throw invalid_argument("win_config out of range");
+    win_config_ = (int)v;
+    win_resident_ = 0;
   } else if (name == "pipe_stages") {
     if (v < 2 || v > 16) throw invalid_argument("pipe_stages must be in 2..16");
     pipe_stages_ = (int)v;
@@ -1335,6 +1418,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "fused_strip") return fused_strip_;
   if (name == "fused_block") return fused_block_;
   if (name == "pipe_stages") return pipe_stages_;
+  if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps_;
   throw invalid_argument("Unknown option '" + name + "'.");
 }

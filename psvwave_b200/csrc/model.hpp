@@ -67,7 +67,7 @@ struct GridArray {
 
 class Model {
  public:
-  static constexpr int kVariantCount = 4;
+  static constexpr int kVariantCount = 5;
   explicit Model(Config cfg, int device);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -141,8 +141,10 @@ class Model {
   void fused_begin(int i_shot, int point_mode);
   int fused_auto_strip(int n_zwarps, int batch);
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
+  void win_geometry(int batch, int *tiles, int *strip);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it);
-  double *F(int k) const { return fld_[cur_][k].data(); }  // current state: vx vz txx tzz txz
+  double *field_ptr(int p, int k) const { return fields_.as<double>() + (size_t)(5 * p + k) * field_stride_ + guard_; }
+  double *F(int k) const { return field_ptr(cur_, k); }  // current state: vx vz txx tzz txz
   void write_wavefield_files(int it);
 
   Config cfg_;
@@ -158,7 +160,8 @@ class Model {
   int n_snap_alloc_ = 0;  // ceil(nt / snapshot_interval)
 
   // grid arrays
-  GridArray fld_[2][5];                       // dynamic fields vx vz txx tzz txz, double-buffered
+  DeviceBuffer fields_;                       // dynamic fields [2 buffers][vx vz txx tzz txz], each padded grid
+  size_t field_stride_ = 0;                   // doubles between consecutive state arrays
   int cur_ = 0;                               // which buffer holds the current state
   GridArray vp_, vs_, rho_, lm_, mu_, b_;     // medium
   DeviceBuffer lame_kernels_;                 // [lambda | mu | density_l], each nx*ld
@@ -182,13 +185,14 @@ class Model {
   double misfit_ = 0.0;
 
   // options / statistics
-  int variant_ = 2;
+  int variant_ = 3;
   bool exact_ = false;
   bool profile_ = false;
   int strip_ = 16, block_ = 128;
   int fused_strip_ = 0 /* 0 = whole waves */, fused_block_ = 128;
   int fused_resident_blocks_ = 0;
-  int pipe_stages_ = 6, pipe_warps_ = 4, pipe_resident_ = 0;
+  int pipe_stages_ = 4, pipe_warps_ = 8, pipe_resident_ = 0;
+  int win_config_ = 0, win_resident_ = 0;
   double stat_elapsed_ms_ = 0, stat_stress_ms_ = 0, stat_velocity_ms_ = 0;
   long long stat_launches_ = 0;
 };
