@@ -66,6 +66,8 @@ struct FusedCommon {
   int parity;       // old state = f[parity], new state = f[parity ^ 1]
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
+  int tile_pairs;   // variant 5: z-pairs per CTA tile
+  int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
   size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
   // snapshots / kernel accumulation
   size_t snap_field_stride;  // n_snap_alloc * nx*ld
@@ -112,10 +114,31 @@ struct RowData {
 };
 
 // Row source of variant 2: straight from global memory (read-only path).
+// Rolling register windows of the march at its first row j = xs - 2.
+struct MarchWindow {
+  double2 vx_m2, vx_m1, vx_0, vx_p1;  // old vx rows j-2 .. j+1
+  double2 vz_m2, vz_m1, vz_0;         // old vz rows j-2 .. j
+};
+
+// Window fill straight from the old state in global memory (variants 2 and 3, stage A of 5).
+__device__ __forceinline__ void window_from_global(const double *ovx, const double *ovz, long long r,
+                                                   long long ld2n, MarchWindow &w) {
+  w.vx_m2 = __ldg(reinterpret_cast<const double2 *>(ovx) + r - 2 * ld2n);
+  w.vx_m1 = __ldg(reinterpret_cast<const double2 *>(ovx) + r - ld2n);
+  w.vx_0 = __ldg(reinterpret_cast<const double2 *>(ovx) + r);
+  w.vx_p1 = __ldg(reinterpret_cast<const double2 *>(ovx) + r + ld2n);
+  w.vz_m2 = __ldg(reinterpret_cast<const double2 *>(ovz) + r - 2 * ld2n);
+  w.vz_m1 = __ldg(reinterpret_cast<const double2 *>(ovz) + r - ld2n);
+  w.vz_0 = __ldg(reinterpret_cast<const double2 *>(ovz) + r);
+}
+
 struct GlobalRows {
   const double *ovx, *ovz, *oxx, *ozz, *oxz, *lm, *mu, *b;
   long long ld2n;
-  __device__ __forceinline__ void fetch(long long r, RowData &d) const {
+  __device__ __forceinline__ void prologue(int, long long r, MarchWindow &w) const {
+    window_from_global(ovx, ovz, r, ld2n, w);
+  }
+  __device__ __forceinline__ void fetch(int, long long r, RowData &d) const {
     d.vx_p2 = ld2s(ovx, r + 2 * ld2n);
     d.vz_p1 = ld2s(ovz, r + ld2n);
     d.txx = ld2s(oxx, r);
@@ -127,22 +150,49 @@ struct GlobalRows {
   }
 };
 
+// What one warp of one stage marches over.
+struct MarchRange {
+  int xs, xe;    // velocities of rows [xs, xe) and stresses of rows [xs-2, xe+2) are computed
+  int mx0, mx1;  // rows whose global side effects (snapshot, correlation, receiver samples) are this CTA's
+  bool own;      // lane computes a pair whose results go to the sink
+  bool mine;     // lane's pair belongs to this CTA's tile (global side effects)
+  int it;        // time index of this stage's step (receiver sample / stf / adjoint-source column)
+};
+
+// Result sink of variants 2 and 3 (and of stage B of variant 5): the new state in global memory.
+struct GlobalSink {
+  double *nvx, *nvz, *nxx, *nzz, *nxz;
+  int xs, xe;
+  bool own;
+  __device__ __forceinline__ void stress(int j, long long r, double2 txx, double2 tzz, double2 txz, double2,
+                                         double2) const {
+    if (own && j >= xs && j < xe) {
+      st2s(nxx, r, txx);
+      st2s(nzz, r, tzz);
+      st2s(nxz, r, txz);
+    }
+  }
+  __device__ __forceinline__ void velocity(int, long long rv, double2 vx, double2 vz, double2) const {
+    if (own) {
+      st2s(nvx, rv, vx);
+      st2s(nvz, rv, vz);
+    }
+  }
+  __device__ __forceinline__ void commit() const {}
+};
+
 // One warp marches rows [xs, xe) for the z-pairs {kp0 + lane}; lanes 2..29 own their pair.
-template <class M, int MODE, class Rows>
-__device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedModel &m, Rows &rows,
-                                            const int lane, const int kp, const int xs, const int xe) {
+template <class M, int MODE, class Rows, class Sink>
+__device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedModel &m, Rows &rows, Sink &sink,
+                                            const int lane, const int kp, const MarchRange rg) {
   const int nx = c.g.nx, nz = c.g.nz;
   const long long ld2n = c.g.ld >> 1;
   const int z0 = kp * 2;
-  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
+  const int xs = rg.xs, xe = rg.xe;
+  const bool own = rg.own, mine = rg.mine;
   const bool za = z0 >= 2 && z0 < nz - 2;
   const bool zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
   const double tza = taper_axis(c.taper_table, c.g.np, z0, nz), tzb = taper_axis(c.taper_table, c.g.np, z0 + 1, nz);
-
-  const double *__restrict__ ovx = m.f[c.parity][0], *__restrict__ ovz = m.f[c.parity][1];
-  double *__restrict__ nvx = m.f[c.parity ^ 1][0], *__restrict__ nvz = m.f[c.parity ^ 1][1];
-  double *__restrict__ nxx = m.f[c.parity ^ 1][2], *__restrict__ nzz = m.f[c.parity ^ 1][3];
-  double *__restrict__ nxz = m.f[c.parity ^ 1][4];
 
   // point operations present in this strip?
   bool strip_rec = false, strip_ops = false;
@@ -155,9 +205,10 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
   int j = xs - 2;
   long long r = (long long)j * ld2n + kp;
   // old velocities: vx rows j-2..j+1 (+ j+2 loaded per iteration), vz rows j-2..j (+ j+1)
-  double2 vx_m2 = ld2s(ovx, r - 2 * ld2n), vx_m1 = ld2s(ovx, r - ld2n), vx_0 = ld2s(ovx, r),
-          vx_p1 = ld2s(ovx, r + ld2n);
-  double2 vz_m2 = ld2s(ovz, r - 2 * ld2n), vz_m1 = ld2s(ovz, r - ld2n), vz_0 = ld2s(ovz, r);
+  MarchWindow w0;
+  rows.prologue(j, r, w0);
+  double2 vx_m2 = w0.vx_m2, vx_m1 = w0.vx_m1, vx_0 = w0.vx_0, vx_p1 = w0.vx_p1;
+  double2 vz_m2 = w0.vz_m2, vz_m1 = w0.vz_m1, vz_0 = w0.vz_0;
   // new stresses: txx rows j-4..j-1, txz rows j-3..j-1, tzz rows j-2..j-1
   const double2 zero2 = make_double2(0.0, 0.0);
   double2 xx_m4 = zero2, xx_m3 = zero2, xx_m2 = zero2, xx_m1 = zero2;
@@ -167,15 +218,15 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
 #pragma unroll 1
   for (; j < xe + 2; ++j, r += ld2n) {
     RowData d;
-    rows.fetch(r, d);
+    rows.fetch(j, r, d);
     const double2 vx_p2 = d.vx_p2, vz_p1 = d.vz_p1;
     double2 txx = d.txx, tzz = d.tzz, txz = d.txz;
     const double2 lm = d.lm, mu = d.mu;
-    const bool row_mine = j >= xs && j < xe;  // warp-uniform
+    const bool row_mine = j >= rg.mx0 && j < rg.mx1;  // warp-uniform
     const double tr_j = taper_axis(c.taper_table, c.g.np, j, nx), tr_x = taper_axis(c.taper_table, c.g.np, j - 2, nx);
 
     if (row_mine) {
-      if (MODE == MODE_SNAPSHOT && own) {
+      if (MODE == MODE_SNAPSHOT && mine) {
         double *s = m.snap + c.snap_offset;
         st2s(s, r, vx_0);
         st2s(s + c.snap_field_stride, r, vz_0);
@@ -184,7 +235,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         st2s(s + 4 * c.snap_field_stride, r, txz);
       }
       if (MODE == MODE_ACCUMULATE) {
-        if (own && j >= c.wx0 && j < c.wx1 && z0 + 1 >= c.wz0 && z0 < c.wz1) {
+        if (mine && j >= c.wx0 && j < c.wx1 && z0 + 1 >= c.wz0 && z0 < c.wz1) {
           const double *s = m.snap + c.snap_offset;
           const double2 fvx = ld2s(s, r), fvz = ld2s(s + c.snap_field_stride, r),
                         fxx = ld2s(s + 2 * c.snap_field_stride, r),
@@ -209,11 +260,11 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         const int q1 = c.rec_row_start[j + 1];
         for (int q = c.rec_row_start[j]; q < q1; ++q) {
           const int z = c.rec_z[q];
-          if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
+          if (mine && (z >> 1) == kp) {
+            const size_t t = (size_t)c.rec_id[q] * c.nt + rg.it;
             const double sx = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vx_0.y : vx_0.x), c.dxdz);
             const double sz = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vz_0.y : vz_0.x), c.dxdz);
-            if (c.it == 0) {
+            if (rg.it == 0) {
               m.ux[t] = sx;
               m.uz[t] = sz;
             } else {
@@ -254,11 +305,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       tzz.y = ub ? bzz : tzz.y;
       txz.y = ub ? bxz : txz.y;
     }
-    if (row_mine && own) {
-      st2s(nxx, r, txx);
-      st2s(nzz, r, tzz);
-      st2s(nxz, r, txz);
-    }
+    sink.stress(j, r, txx, tzz, txz, lm, mu);
 
     // ---- velocity update of row x = j-2 (new stresses: txx x-2..x+1, txz x-1..x+2, tzz x) ----
     const int x = j - 2;
@@ -297,7 +344,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         for (int q = c.op_row_start[x]; q < q1; ++q) {
           const RowOp op = c.ops[q];
           if (own && (op.z >> 1) == kp) {
-            const double w = c.stf[(size_t)op.source * c.nt + c.it];
+            const double w = c.stf[(size_t)op.source * c.nt + rg.it];
             const double bb = (op.z & 1) ? b.y : b.x;
             const double amp = __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(op.weight, w), c.dt), bb), op.d4);
             const bool odd = op.z & 1;
@@ -317,7 +364,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         for (int q = c.rec_row_start[x]; q < q1; ++q) {
           const int z = c.rec_z[q];
           if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
+            const size_t t = (size_t)c.rec_id[q] * c.nt + rg.it;
             const double bb = (z & 1) ? b.y : b.x;
             const double ax = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.ax[t]), c.dxdz);
             const double az = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.az[t]), c.dxdz);
@@ -331,11 +378,9 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
           }
         }
       }
-      if (own) {
-        st2s(nvx, rv, vx);
-        st2s(nvz, rv, vz);
-      }
+      sink.velocity(x, rv, vx, vz, b);
     }
+    sink.commit();
 
     // rotate the windows
     vx_m2 = vx_m1; vx_m1 = vx_0; vx_0 = vx_p1; vx_p1 = vx_p2;
@@ -358,7 +403,10 @@ __global__ void __launch_bounds__(128) fused_step_kernel(const FusedCommon c,
   const int xe = min(xs + c.strip, c.g.nx);
   GlobalRows rows{m.f[c.parity][0], m.f[c.parity][1], m.f[c.parity][2], m.f[c.parity][3], m.f[c.parity][4],
                   m.lm, m.mu, m.b, (long long)(c.g.ld >> 1)};
-  fused_march<M, MODE>(c, m, rows, lane, kp, xs, xe);
+  const bool own = lane >= 2 && lane < 30 && kp < (c.g.ld >> 1);
+  GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
+                  m.f[c.parity ^ 1][4], xs, xe, own};
+  fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xs, xe, xs, xe, own, own, c.it});
 }
 
 // ------------------------------------------------------------------------------------------
@@ -421,7 +469,12 @@ struct PipeRows {
   int slot;
   unsigned phase;
   int lane;
-  __device__ __forceinline__ void fetch(long long, RowData &d) {
+  const double *ovx, *ovz;    // old velocities in global memory (window fill)
+  long long ld2n;
+  __device__ __forceinline__ void prologue(int, long long r, MarchWindow &w) const {
+    window_from_global(ovx, ovz, r, ld2n, w);
+  }
+  __device__ __forceinline__ void fetch(int, long long, RowData &d) {
     mbar_wait(full0 + 8 * slot, phase);
     const unsigned char *s = ring + (size_t)slot * stage_bytes + lane_off;
     d.vx_p2 = *reinterpret_cast<const double2 *>(s);
@@ -496,9 +549,13 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
   }
 
   // ---- consumers ----
-  PipeRows rows{ring, full0, empty0, stages, G::kSeg, G::kStage, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane};
+  PipeRows rows{ring, full0, empty0, stages, G::kSeg, G::kStage, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane,
+                m.f[c.parity][0], m.f[c.parity][1], ld2n};
   const int kp = kp_tile + warp * kFusedOwnedPairs + lane;
-  fused_march<M, MODE>(c, m, rows, lane, kp, xs, xe);
+  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
+  GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
+                  m.f[c.parity ^ 1][4], xs, xe, own};
+  fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xs, xe, xs, xe, own, own, c.it});
 }
 
 }  // namespace psv

@@ -13,6 +13,7 @@
 #include "fused.cuh"
 #include "kernels.cuh"
 #include "pointwise.cuh"
+#include "pair.cuh"
 #include "window.cuh"
 
 namespace psv {
@@ -689,7 +690,74 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
   }
 }
 
-void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it) {
+// ---- variant 5: two time steps per launch (pair.cuh) -------------------------------------------
+namespace {
+constexpr size_t kMaxDynamicSmem = 232448;  // 227 KB per CTA on sm_100
+
+template <class M, int MODE, int NW>
+void launch_pair_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
+                   cudaStream_t st) {
+  static size_t configured = 0;  // per instantiation
+  if (configured < smem) {
+    PSV_CUDA(cudaFuncSetAttribute(fused_pair_kernel<M, MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    configured = smem;
+  }
+  fused_pair_kernel<M, MODE, NW><<<grid, 2 * NW * 32, smem, st>>>(fc, models, stages);
+}
+template <class M, int NW>
+void launch_pair_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
+                   cudaStream_t st) {
+  if (mode == MODE_SNAPSHOT) launch_pair_k<M, MODE_SNAPSHOT, NW>(fc, models, grid, stages, smem, st);
+  else if (mode == MODE_ACCUMULATE) launch_pair_k<M, MODE_ACCUMULATE, NW>(fc, models, grid, stages, smem, st);
+  else launch_pair_k<M, MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
+}
+template <class M>
+void launch_pair(int nw, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages,
+                 size_t smem, cudaStream_t st) {
+  if (nw == 4) launch_pair_m<M, 4>(mode, fc, models, grid, stages, smem, st);
+  else launch_pair_m<M, 6>(mode, fc, models, grid, stages, smem, st);
+}
+size_t pair_smem(int nw, int stages) {
+  return nw == 4 ? pair_smem_bytes<4>(stages) : pair_smem_bytes<6>(stages);
+}
+}  // namespace
+
+// Launch geometry of variant 5: even z-tiles over the pairs that hold real columns, and rows per
+// CTA such that the launch is a whole number of waves (one CTA per SM: the rings fill its smem).
+void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem) {
+  const int nw = pair_warps_;
+  const int max_tile = nw * kFusedOwnedPairs - 4;
+  const int pairs = (cfg_.nz + 1) / 2;
+  *tiles = (pairs + max_tile - 1) / max_tile;
+  *tile_pairs = (pairs + *tiles - 1) / *tiles;
+  int stages = pair_stages_;
+  if (stages == 0) {
+    stages = 4;
+    while (stages > 2 && pair_smem(nw, stages) > kMaxDynamicSmem) --stages;
+  }
+  *smem = pair_smem(nw, stages);
+  if (*smem > kMaxDynamicSmem) throw invalid_argument("pair_stages: the rings do not fit in shared memory");
+  pair_stages_ = stages;
+  if (pair_strip_ > 0) {
+    *strip = pair_strip_;
+    return;
+  }
+  int sms = 0;
+  PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+  const int blocks_x = *tiles * batch;
+  const int nx = cfg_.nx;
+  for (int waves = 1;; ++waves) {
+    const int n_strips = std::max(1, waves * sms / blocks_x);
+    const int st = (nx + n_strips - 1) / n_strips;
+    if (st <= 192 || n_strips >= nx) {
+      *strip = std::max(st, 8);
+      return;
+    }
+  }
+}
+
+void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
   const Config &c = cfg_;
   FusedCommon fc{};
   fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
@@ -699,6 +767,8 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.field_stride = field_stride_;
   fc.n_zwarps = (ld_ / 2 + kFusedOwnedPairs - 1) / kFusedOwnedPairs;
   fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1));
+  fc.tile_pairs = 0;
+  fc.it_step = 0;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
   fc.wx0 = c.np_boundary + c.nx_inner_boundary;
@@ -718,14 +788,25 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.ops = plans_[i_shot].row_ops.as<RowOp>();
   fc.stf = stf_.as<>();
   const FusedModel *models = fused_model_.as<FusedModel>();
-  if (variant_ == 4) {
+  if (variant_ == 5 && pair_step != 0) {
+    int tiles = 0, tile_pairs = 0, strip = 0;
+    size_t smem = 0;
+    pair_geometry(1, &tiles, &tile_pairs, &strip, &smem);
+    fc.strip = strip;
+    fc.tile_pairs = tile_pairs;
+    fc.it_step = pair_step;
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
+    if (exact_) launch_pair<ExactMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
+    else launch_pair<FastMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
+    ++stat_pair_launches_;
+  } else if (variant_ == 4) {
     int tiles = 0, strip = 0;
     win_geometry(1, &tiles, &strip);
     fc.strip = strip;
     dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
     if (exact_) launch_win<ExactMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
     else launch_win<FastMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
-  } else if (variant_ == 3) {
+  } else if (variant_ == 3 || variant_ == 5) {
     int tiles = 0, strip = 0;
     size_t smem = 0;
     pipe_geometry(1, &tiles, &strip, &smem);
@@ -800,6 +881,7 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   if (store_fields) ensure_snapshots(i_shot);
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
+  stat_pair_launches_ = 0;
   zero_dynamic_fields();
   PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
   Profiler prof(prof_events_, stream_, profile_, c.nt);
@@ -815,15 +897,20 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   for (int it = 0; it < c.nt; ++it) {
     if (variant_ >= 2) {
       const bool snap = store_fields && it % c.snapshot_interval == 0;
-      const bool sample = prof.sample(snap);
+      // variant 5 advances two steps per launch unless the second one has a snapshot to store
+      const bool pair = variant_ == 5 && !output_wavefields && it + 1 < c.nt &&
+                        !(store_fields && (it + 1) % c.snapshot_interval == 0);
+      const bool sample = prof.sample(snap || (variant_ == 5 && !pair));
       if (sample) prof.mark(0);
-      launch_fused(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, POINT_FORWARD, i_shot, it / c.snapshot_interval, it);
+      launch_fused(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, POINT_FORWARD, i_shot, it / c.snapshot_interval, it,
+                   pair ? 1 : 0);
       if (sample) {
         prof.mark(1);
         prof.mark(2);
         prof.next();
       }
       if (output_wavefields && it % 10 == 0) write_wavefield_files(it);
+      if (pair) ++it;
       continue;
     }
     // the point kernels take the state pointers per step (the fused variant may have left the
@@ -877,6 +964,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
                       "forward_simulate(i_shot, store_fields=True) first.");
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
+  stat_pair_launches_ = 0;
   zero_dynamic_fields();
   PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
   Profiler prof(prof_events_, stream_, profile_, c.nt);
@@ -888,16 +976,19 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   if (variant_ >= 2) fused_begin(i_shot, POINT_ADJOINT);
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
-    const bool sample = prof.sample(corr);
+    // variant 5 retreats two steps per launch unless the second one correlates with a snapshot
+    const bool pair = variant_ == 5 && it - 1 >= 0 && (it - 1) % c.snapshot_interval != 0;
+    const bool sample = prof.sample(corr || (variant_ == 5 && !pair));
     if (variant_ >= 2) {
       if (sample) prof.mark(0);
       launch_fused(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, c.nr > 0 ? POINT_ADJOINT : POINT_NONE, i_shot,
-                   it / c.snapshot_interval, it);
+                   it / c.snapshot_interval, it, pair ? -1 : 0);
       if (sample) {
         prof.mark(1);
         prof.mark(2);
         prof.next();
       }
+      if (pair) --it;
       continue;
     }
     if (sample) prof.mark(0);
@@ -1397,6 +1488,16 @@ void Model::set_option(const std::string &name, long long v) {
     if (v != 4 && v != 8) throw invalid_argument("pipe_warps must be 4 or 8");
     pipe_warps_ = (int)v;
     pipe_resident_ = 0;
+  } else if (name == "pair_warps") {
+    if (v != 4 && v != 6) throw invalid_argument("pair_warps must be 4 or 6");
+    pair_warps_ = (int)v;
+    pair_stages_ = 0;
+  } else if (name == "pair_stages") {
+    if (v < 0 || v > 8) throw invalid_argument("pair_stages must be in 0..8 (0 = as many as fit)");
+    pair_stages_ = (int)v;
+  } else if (name == "pair_strip") {
+    if (v < 0) throw invalid_argument("pair_strip must be >= 0 (0 = whole waves)");
+    pair_strip_ = (int)v;
   } else if (name == "fused_block") {
     if (v != 32 && v != 64 && v != 128) throw invalid_argument("fused_block must be 32, 64 or 128");
     fused_block_ = (int)v;
@@ -1420,6 +1521,9 @@ long long Model::get_option(const std::string &name) const {
   if (name == "pipe_stages") return pipe_stages_;
   if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps_;
+  if (name == "pair_warps") return pair_warps_;
+  if (name == "pair_stages") return pair_stages_;
+  if (name == "pair_strip") return pair_strip_;
   throw invalid_argument("Unknown option '" + name + "'.");
 }
 
@@ -1428,6 +1532,7 @@ double Model::get_stat(const std::string &name) const {
   if (name == "launches") return (double)stat_launches_;
   if (name == "stress_ms") return stat_stress_ms_;
   if (name == "velocity_ms") return stat_velocity_ms_;
+  if (name == "pair_launches") return (double)stat_pair_launches_;
   if (name == "pitch") return ld_;
   if (name == "snapshot_bytes_per_shot") return 5.0 * n_snap_alloc_ * (double)grid_elems_ * sizeof(double);
   throw invalid_argument("Unknown statistic '" + name + "'.");

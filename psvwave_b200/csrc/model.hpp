@@ -67,7 +67,7 @@ struct GridArray {
 
 class Model {
  public:
-  static constexpr int kVariantCount = 5;
+  static constexpr int kVariantCount = 6;
   explicit Model(Config cfg, int device);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -142,7 +142,8 @@ class Model {
   int fused_auto_strip(int n_zwarps, int batch);
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
   void win_geometry(int batch, int *tiles, int *strip);
-  void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it);
+  void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
+  void pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem);
   double *field_ptr(int p, int k) const { return fields_.as<double>() + (size_t)(5 * p + k) * field_stride_ + guard_; }
   double *F(int k) const { return field_ptr(cur_, k); }  // current state: vx vz txx tzz txz
   void write_wavefield_files(int it);
@@ -193,6 +194,9 @@ class Model {
   int fused_resident_blocks_ = 0;
   int pipe_stages_ = 4, pipe_warps_ = 8, pipe_resident_ = 0;
   int win_config_ = 0, win_resident_ = 0;
+  int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
+  long long stat_pair_launches_ = 0;
+  double stat_pair_ms_ = 0;
   double stat_elapsed_ms_ = 0, stat_stress_ms_ = 0, stat_velocity_ms_ = 0;
   long long stat_launches_ = 0;
 };
