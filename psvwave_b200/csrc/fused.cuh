@@ -30,6 +30,8 @@
 // pointers); geometry, point-operation lists and the time index are shared by the batch.
 #pragma once
 
+#include <cstdio>
+
 #include "kernels.cuh"
 #include "pointwise.cuh"
 
@@ -433,6 +435,22 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+#ifdef PSV_DEBUG_WAIT
+// Debug build: bounded spin, then report who waits for what and carry on (results are garbage).
+__device__ __noinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  for (int spin = 0; spin < 400000; ++spin) {
+    unsigned ok;
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) return;
+  }
+  printf("mbar timeout: block (%d,%d) warp %d lane %d bar-index %u parity %u\n", blockIdx.x, blockIdx.y,
+         threadIdx.x >> 5, threadIdx.x & 31, (bar & 0xffffu) / 8, parity);
+}
+#else
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
   asm volatile(
       "{\n"
@@ -446,6 +464,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
       "r"(parity)
       : "memory");
 }
+#endif
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)

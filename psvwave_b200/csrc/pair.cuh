@@ -67,9 +67,13 @@ struct SlotSink {
   int lane;
   bool own;
   bool acquired;
+  bool wrapped;  // false during the first pass over the ring: nothing to wait for.  (The usual
+                 // "wait for parity 1 on a fresh barrier" shortcut is wrong here: stage B hands
+                 // back the slots it skips before stage A ever touches them, which completes
+                 // phase 0 early and would leave a parity-1 wait hanging.)
   __device__ __forceinline__ void acquire() {
     if (!acquired) {
-      mbar_wait(empty0 + 8 * slot, phase ^ 1);
+      if (wrapped) mbar_wait(empty0 + 8 * slot, phase ^ 1);
       acquired = true;
     }
   }
@@ -100,6 +104,7 @@ struct SlotSink {
     if (++slot == kPairSlots) {
       slot = 0;
       phase ^= 1;
+      wrapped = true;
     }
   }
 };
@@ -268,7 +273,7 @@ __global__ void __launch_bounds__(2 * NW * 32) fused_pair_kernel(const FusedComm
     const bool own = lane >= 2 && lane < 30;
     const bool mine = own && kp >= tb0 && kp < tb0 + c.tile_pairs && kp < (int)ld2n;
     SlotSink sink{ring_x, full_x, empty_x, G::kSegX, G::kSlotX, (warp * kFusedOwnedPairs + lane - 2) * 16,
-                  0,      0u,     lane,    own,      false};
+                  0,      0u,     lane,    own,      false, false};
     fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xsA, xeA, xs, xe, own, mine, c.it});
     return;
   }
