@@ -361,6 +361,10 @@ def run_ours(args) -> None:
         if fused:
             ms = float(P[:, [0, 2]].mean())
             kern, nbytes = "fused stress+velocity sweep", bytes_per_launch["fused"]
+            if m._get_option("variant") == 5:
+                # the sampled launches of variant 5 are its two-step launches: 2 grid-point updates
+                # per point, each credited with the single-pass 128 B
+                kern, nbytes = "fused two-step sweep", 2 * bytes_per_launch["fused"]
         else:
             s_ms, v_ms = float(P[:, [0, 2]].mean()), float(P[:, [1, 3]].mean())
             if s_ms >= v_ms:
