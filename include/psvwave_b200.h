@@ -194,6 +194,15 @@ int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out);
  * used by the host layer for the cross-rank sum (one all-reduce) over NCCL. */
 int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count);
 int psv_synchronize(psv_handle h);
+/* Monte-Carlo ensembles (SURVEY 8e "replicas only"; the reference's route is n independent copies of
+ * the object, src/fdModel.cpp:64-97, each simulated on its own).  The n models must describe one
+ * experiment on one device (same grid, time axis, boundary, sources, receivers, snapshot interval);
+ * media differ.  All n models advance through forward_simulate / adjoint_simulate of shot i_shot
+ * together, one kernel launch per time step for the whole ensemble, and end in exactly the state n
+ * separate psv_forward_simulate / psv_adjoint_simulate calls would leave.  Tuning options are
+ * those of handles[0].  Needs a fused variant (>= 2, the default). */
+int psv_forward_batch(const psv_handle *handles, int n, int i_shot, int store_fields);
+int psv_adjoint_batch(const psv_handle *handles, int n, int i_shot);
 /* Device stopwatch on the model's stream (CUDA events): start records an event, stop records a
  * second one, waits for it and returns the milliseconds between the two. */
 int psv_timer_start(psv_handle h);

@@ -3,6 +3,7 @@
 #include <cstring>
 #include <sstream>
 #include <string>
+#include <vector>
 
 #include "model.hpp"
 
@@ -364,6 +365,29 @@ int psv_load_model(psv_handle h, const char *de_path, const char *vp_path, const
 }
 int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, size_t n) {
   return guarded([&] { model(h).load_vector(path, verbose != 0, out, n); });
+}
+
+namespace {
+std::vector<psv::Model *> batch_models(const psv_handle *handles, int n) {
+  if (!handles || n < 1) throw psv::invalid_argument("Batched simulate needs at least one model.");
+  std::vector<psv::Model *> v(n);
+  for (int i = 0; i < n; ++i) v[i] = &model(handles[i]);
+  return v;
+}
+}  // namespace
+
+int psv_forward_batch(const psv_handle *handles, int n, int i_shot, int store_fields) {
+  return guarded([&] {
+    const std::vector<psv::Model *> v = batch_models(handles, n);
+    psv::Model::forward_batch(v.data(), n, i_shot, store_fields != 0);
+  });
+}
+
+int psv_adjoint_batch(const psv_handle *handles, int n, int i_shot) {
+  return guarded([&] {
+    const std::vector<psv::Model *> v = batch_models(handles, n);
+    psv::Model::adjoint_batch(v.data(), n, i_shot);
+  });
 }
 
 int psv_release_snapshots(psv_handle h, int i_shot) {

@@ -187,7 +187,8 @@ struct GlobalSink {
 template <class M, int MODE, class Rows, class Sink>
 __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedModel &m, Rows &rows, Sink &sink,
                                             const int lane, const int kp, const MarchRange rg) {
-  const int nx = c.g.nx, nz = c.g.nz;
+  const int nz = c.g.nz;
+  const int gx0 = c.g.x_off, gnx = c.g.nx_global;  // rows of a slab count from gx0 in the whole grid
   const long long ld2n = c.g.ld >> 1;
   const int z0 = kp * 2;
   const int xs = rg.xs, xe = rg.xe;
@@ -225,7 +226,8 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
     double2 txx = d.txx, tzz = d.tzz, txz = d.txz;
     const double2 lm = d.lm, mu = d.mu;
     const bool row_mine = j >= rg.mx0 && j < rg.mx1;  // warp-uniform
-    const double tr_j = taper_axis(c.taper_table, c.g.np, j, nx), tr_x = taper_axis(c.taper_table, c.g.np, j - 2, nx);
+    const double tr_j = taper_axis(c.taper_table, c.g.np, gx0 + j, gnx),
+                 tr_x = taper_axis(c.taper_table, c.g.np, gx0 + j - 2, gnx);
 
     if (row_mine) {
       if (MODE == MODE_SNAPSHOT && mine) {
@@ -283,7 +285,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
     {
       const double vxL_y = shfl_up1(vx_0.y), vxR_x = shfl_dn1(vx_0.x), vxR_y = shfl_dn1(vx_0.y);
       const double vzL_x = shfl_up1(vz_0.x), vzL_y = shfl_up1(vz_0.y), vzR_x = shfl_dn1(vz_0.x);
-      const bool rowok = j >= 2 && j < nx - 2;
+      const bool rowok = gx0 + j >= 2 && gx0 + j < gnx - 2;
       double axx = txx.x, azz = tzz.x, axz = txz.x, bxx = txx.y, bzz = tzz.y, bxz = txz.y;
       {  // point (j, z0)
         const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
@@ -318,7 +320,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       {
         const double xzL_x = shfl_up1(xz_m2.x), xzL_y = shfl_up1(xz_m2.y), xzR_x = shfl_dn1(xz_m2.x);
         const double zzL_y = shfl_up1(zz_m2.y), zzR_x = shfl_dn1(zz_m2.x), zzR_y = shfl_dn1(zz_m2.y);
-        const bool rowok = x >= 2 && x < nx - 2;
+        const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
         double avx = vx.x, avz = vz.x, bvx = vx.y, bvz = vz.y;
         {
           const double dxm_txx = diff4<M>(c.k, xx_m2.x, xx_m3.x, xx_m4.x, xx_m1.x);

@@ -26,6 +26,9 @@ enum SweepMode { MODE_PLAIN = 0, MODE_SNAPSHOT = 1, MODE_ACCUMULATE = 2 };
 struct GridShape {
   int nx, nz, ld;  // ld = row pitch in doubles (even, multiple of 16)
   int np;          // taper width
+  // x-slab of a larger grid (domain split, fused variants only): local row j is row j + x_off of
+  // a grid of nx_global rows.  A whole grid has x_off = 0, nx_global = nx.
+  int x_off, nx_global;
 };
 
 struct StressArgs {

@@ -503,7 +503,7 @@ void Model::launch_velocity(double sdt) {
 }
 
 // ---- variant 2: one fused launch per time step ------------------------------------------------
-void Model::fused_begin(int i_shot, int point_mode) {
+void Model::fill_fused_model(int i_shot, void *out) const {
   const Config &c = cfg_;
   FusedModel fm{};
   for (int p = 0; p < 2; ++p)
@@ -520,10 +520,19 @@ void Model::fused_begin(int i_shot, int point_mode) {
   fm.uz = rtf_uz_.as<>() + shot_rows;
   fm.ax = a_stf_ux_.as<>() + shot_rows;
   fm.az = a_stf_uz_.as<>() + shot_rows;
+  *static_cast<FusedModel *>(out) = fm;
+}
+
+// Device copy of the per-model pointers: this model first, then the followers of a batch.
+void Model::fused_begin(int i_shot, int point_mode) {
   (void)point_mode;
-  if (fused_model_.empty()) fused_model_.allocate(sizeof(FusedModel));
-  // stream-ordered upload from a stack object: wait for it before the object dies
-  copy_sync(fused_model_.as<FusedModel>(), &fm, sizeof(FusedModel), cudaMemcpyHostToDevice);
+  std::vector<FusedModel> fm(1 + batch_followers_.size());
+  fill_fused_model(i_shot, &fm[0]);
+  for (size_t i = 0; i < batch_followers_.size(); ++i) batch_followers_[i]->fill_fused_model(i_shot, &fm[i + 1]);
+  const size_t bytes = fm.size() * sizeof(FusedModel);
+  if (fused_model_.bytes() < bytes) fused_model_.allocate(bytes);
+  // stream-ordered upload from a local object: wait for it before the object dies
+  copy_sync(fused_model_.as<FusedModel>(), fm.data(), bytes, cudaMemcpyHostToDevice);
 }
 
 namespace {
@@ -653,24 +662,45 @@ void Model::win_geometry(int batch, int *tiles, int *strip) {
 
 // Launch geometry of variant 3: CTAs per row, and rows per CTA such that the launch is a whole
 // number of waves of resident CTAs.
+namespace {
+template <int NW>
+int pipe_occupancy(size_t smem) {
+  int per_sm = 0;
+  PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, NW>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, NW>,
+                                                         (NW + 1) * 32, smem));
+  return per_sm;
+}
+}  // namespace
+
+// Consumer warps per CTA of variant 3: the compiled width (8, 4 or 3 warps of 28 pairs) that covers
+// a row with the fewest warps; wide rows tie and take 8, the 80-pair rows of the default
+// configuration take 3 (84 pairs) instead of leaving 5 of 8 warps idle.
+int Model::pipe_warps() const {
+  if (pipe_warps_ != 0) return pipe_warps_;
+  int best = 8, cost = 1 << 30;
+  for (int nw : {8, 4, 3}) {
+    const int owned = nw * kFusedOwnedPairs;
+    const int c = ((ld_ / 2 + owned - 1) / owned) * nw;
+    if (c < cost) {
+      cost = c;
+      best = nw;
+    }
+  }
+  return best;
+}
+
 void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
-  const int nw = pipe_warps_;
+  const int nw = pipe_warps();
   const int owned = nw * kFusedOwnedPairs;
   *tiles = (ld_ / 2 + owned - 1) / owned;
-  *smem = nw == 8 ? pipe_smem_bytes<8>(pipe_stages_) : pipe_smem_bytes<4>(pipe_stages_);
+  *smem = nw == 8 ? pipe_smem_bytes<8>(pipe_stages_) : nw == 4 ? pipe_smem_bytes<4>(pipe_stages_)
+                                                                 : pipe_smem_bytes<3>(pipe_stages_);
   if (pipe_resident_ == 0) {
-    int per_sm = 0, sms = 0;
-    if (nw == 8) {
-      PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, 8>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
-      PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, 8>,
-                                                             (nw + 1) * 32, *smem));
-    } else {
-      PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, 4>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
-      PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, 4>,
-                                                             (nw + 1) * 32, *smem));
-    }
+    int sms = 0;
+    const int per_sm = nw == 8 ? pipe_occupancy<8>(*smem) : nw == 4 ? pipe_occupancy<4>(*smem)
+                                                                      : pipe_occupancy<3>(*smem);
     PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
     pipe_resident_ = std::max(1, per_sm * sms);
   }
@@ -766,7 +796,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.parity = cur_;
   fc.field_stride = field_stride_;
   fc.n_zwarps = (ld_ / 2 + kFusedOwnedPairs - 1) / kFusedOwnedPairs;
-  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1));
+  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1 + (int)batch_followers_.size()));
   fc.tile_pairs = 0;
   fc.it_step = 0;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
@@ -788,40 +818,45 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.ops = plans_[i_shot].row_ops.as<RowOp>();
   fc.stf = stf_.as<>();
   const FusedModel *models = fused_model_.as<FusedModel>();
+  const int batch = 1 + (int)batch_followers_.size();
   if (variant_ == 5 && pair_step != 0) {
     int tiles = 0, tile_pairs = 0, strip = 0;
     size_t smem = 0;
-    pair_geometry(1, &tiles, &tile_pairs, &strip, &smem);
+    pair_geometry(batch, &tiles, &tile_pairs, &strip, &smem);
     fc.strip = strip;
     fc.tile_pairs = tile_pairs;
     fc.it_step = pair_step;
-    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
     if (exact_) launch_pair<ExactMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
     else launch_pair<FastMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
     ++stat_pair_launches_;
   } else if (variant_ == 4) {
     int tiles = 0, strip = 0;
-    win_geometry(1, &tiles, &strip);
+    win_geometry(batch, &tiles, &strip);
     fc.strip = strip;
-    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
     if (exact_) launch_win<ExactMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
     else launch_win<FastMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
   } else if (variant_ == 3 || variant_ == 5) {
     int tiles = 0, strip = 0;
     size_t smem = 0;
-    pipe_geometry(1, &tiles, &strip, &smem);
+    pipe_geometry(batch, &tiles, &strip, &smem);
     fc.strip = strip;
-    dim3 grid(tiles, (c.nx + strip - 1) / strip, 1);
-    if (pipe_warps_ == 8) {
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
+    const int nw = pipe_warps();
+    if (nw == 8) {
       if (exact_) launch_pipe_m<ExactMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
       else launch_pipe_m<FastMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
-    } else {
+    } else if (nw == 4) {
       if (exact_) launch_pipe_m<ExactMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
       else launch_pipe_m<FastMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+    } else {
+      if (exact_) launch_pipe_m<ExactMath, 3>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      else launch_pipe_m<FastMath, 3>(mode, fc, models, grid, pipe_stages_, smem, stream_);
     }
   } else {
     const int wpb = fused_block_ / 32;
-    dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, 1);
+    dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
     if (exact_) launch_fused_m<ExactMath>(mode, fc, models, grid, fused_block_, stream_);
     else launch_fused_m<FastMath>(mode, fc, models, grid, fused_block_, stream_);
   }
@@ -1016,6 +1051,88 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
     std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
   }
+}
+
+// ---- Monte-Carlo ensembles: n models of one experiment, one launch per time step ---------------
+// The reference runs such ensembles as independent fdModel copies (copy ctor src/fdModel.cpp:64-97,
+// SURVEY 8a20/8e); here they share the launches, nothing else.
+void Model::check_batch(Model *const *models, int n, int i_shot) {
+  if (!models || n < 1) throw invalid_argument("Batched simulate needs at least one model.");
+  for (int i = 0; i < n; ++i)
+    if (!models[i]) throw invalid_argument("Null model in the batch.");
+  const Model &a = *models[0];
+  a.check_shot(i_shot);
+  if (a.variant_ < 2) throw invalid_argument("Batched simulate needs a fused variant (variant >= 2).");
+  for (int i = 1; i < n; ++i) {
+    const Model &b = *models[i];
+    for (int k = 0; k < i; ++k)
+      if (models[k] == models[i]) throw invalid_argument("The same model appears twice in the batch.");
+    const Config &p = a.cfg_, &q = b.cfg_;
+    const bool same = b.device_ == a.device_ && p.nx == q.nx && p.nz == q.nz && p.nt == q.nt && p.dx == q.dx &&
+                      p.dz == q.dz && p.dt == q.dt && p.np_boundary == q.np_boundary && p.np_factor == q.np_factor &&
+                      p.nx_inner_boundary == q.nx_inner_boundary && p.nz_inner_boundary == q.nz_inner_boundary &&
+                      p.snapshot_interval == q.snapshot_interval && p.peak_frequency == q.peak_frequency &&
+                      p.delay_cycles_per_shot == q.delay_cycles_per_shot && p.ix_sources == q.ix_sources &&
+                      p.iz_sources == q.iz_sources && p.moment_angles == q.moment_angles &&
+                      p.which_source_to_fire_in_which_shot == q.which_source_to_fire_in_which_shot &&
+                      p.ix_receivers == q.ix_receivers && p.iz_receivers == q.iz_receivers;
+    if (!same)
+      throw invalid_argument("Batched simulate needs models of one experiment on one device: same grid, time axis, "
+                             "boundary, sources, receivers and snapshot interval.");
+  }
+}
+
+void Model::adopt_batch_state(const Model &leader) {
+  cur_ = leader.cur_;
+  stat_launches_ = leader.stat_launches_;
+  stat_pair_launches_ = leader.stat_pair_launches_;
+  stat_elapsed_ms_ = leader.stat_elapsed_ms_;
+  stat_stress_ms_ = leader.stat_stress_ms_;
+  stat_velocity_ms_ = leader.stat_velocity_ms_;
+}
+
+void Model::forward_batch(Model *const *models, int n, int i_shot, bool store_fields) {
+  check_batch(models, n, i_shot);
+  Model &lead = *models[0];
+  lead.bind();
+  for (int i = 1; i < n; ++i) {  // the followers' own streams hand over to the leader's
+    Model &f = *models[i];
+    if (store_fields) f.ensure_snapshots(i_shot);
+    f.zero_dynamic_fields();
+    PSV_CUDA(cudaStreamSynchronize(f.stream_));
+  }
+  lead.batch_followers_.assign(models + 1, models + n);
+  try {
+    lead.forward_simulate(i_shot, store_fields, false, false);
+  } catch (...) {
+    lead.batch_followers_.clear();
+    throw;
+  }
+  lead.batch_followers_.clear();
+  for (int i = 1; i < n; ++i) models[i]->adopt_batch_state(lead);
+}
+
+void Model::adjoint_batch(Model *const *models, int n, int i_shot) {
+  check_batch(models, n, i_shot);
+  Model &lead = *models[0];
+  lead.bind();
+  for (int i = 1; i < n; ++i) {
+    Model &f = *models[i];
+    if (f.snapshots_[i_shot].empty())
+      throw state_error("adjoint_simulate needs the forward wavefield of this shot in every model of the batch: "
+                        "run the stored forward simulation first.");
+    f.zero_dynamic_fields();
+    PSV_CUDA(cudaStreamSynchronize(f.stream_));
+  }
+  lead.batch_followers_.assign(models + 1, models + n);
+  try {
+    lead.adjoint_simulate(i_shot, false);
+  } catch (...) {
+    lead.batch_followers_.clear();
+    throw;
+  }
+  lead.batch_followers_.clear();
+  for (int i = 1; i < n; ++i) models[i]->adopt_batch_state(lead);
 }
 
 // fdModel::run_model (src/fdModel.cpp:1291-1308)
@@ -1485,8 +1602,9 @@ void Model::set_option(const std::string &name, long long v) {
     pipe_stages_ = (int)v;
     pipe_resident_ = 0;
   } else if (name == "pipe_warps") {
-    if (v != 4 && v != 8) throw invalid_argument("pipe_warps must be 4 or 8");
+    if (v != 0 && v != 3 && v != 4 && v != 8) throw invalid_argument("pipe_warps must be 0 (auto), 3, 4 or 8");
     pipe_warps_ = (int)v;
+    pipe_resident_ = 0;
     pipe_resident_ = 0;
   } else if (name == "pair_warps") {
     if (v != 4 && v != 6) throw invalid_argument("pair_warps must be 4 or 6");
@@ -1520,7 +1638,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "fused_block") return fused_block_;
   if (name == "pipe_stages") return pipe_stages_;
   if (name == "win_config") return win_config_;
-  if (name == "pipe_warps") return pipe_warps_;
+  if (name == "pipe_warps") return pipe_warps();
   if (name == "pair_warps") return pair_warps_;
   if (name == "pair_stages") return pair_stages_;
   if (name == "pair_strip") return pair_strip_;

@@ -65,6 +65,14 @@ struct GridArray {
   size_t guard = 0;
 };
 
+// x-slab of a larger grid (SURVEY 8e "large single grids"): global rows [x0, x1) including
+// halo_lo / halo_hi rows that belong to the neighbouring slabs.
+struct SlabSpec {
+  int x0 = 0, x1 = 0, halo_lo = 0, halo_hi = 0;
+};
+// Even split of nx_global rows over nranks slabs, each widened by `halo` rows towards its neighbours.
+SlabSpec slab_partition(int nx_global, int rank, int nranks, int halo);
+
 class Model {
  public:
   static constexpr int kVariantCount = 6;
@@ -85,6 +93,22 @@ class Model {
   void map_kernels_to_velocity();
   void update_from_velocity();
   void run_model(bool verbose, bool simulate_adjoint);
+  // Monte-Carlo ensembles (SURVEY 8e "replicas only", config C4): n models that share one
+  // experiment (grid, time axis, sources, receivers) advance together, ONE launch per time step
+  // for the whole ensemble (blockIdx.z = model).  Each model keeps its own medium, fields,
+  // seismograms, snapshots and kernels; results are those of n separate simulate calls.
+  // Domain split: the time loop in pieces, so that the host layer can exchange halos between
+  // them (psv_march_* / psv_halo_* in the C ABI).  Fused variants 2 and 3 only.
+  void march_begin(int i_shot, bool adjoint, bool store_fields);
+  int march_steps(int n);  // enqueues up to n time steps, returns how many (0 = the loop is done)
+  void march_end();
+  void halo_pack();    // owned edge rows of the 5 fields -> send buffers
+  void halo_unpack();  // receive buffers -> halo rows of the 5 fields
+  void halo_buffers(void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) const;
+  void slab_info(long long out[7]) const;
+  cudaStream_t stream() const { return stream_; }
+  static void forward_batch(Model *const *models, int n, int i_shot, bool store_fields);
+  static void adjoint_batch(Model *const *models, int n, int i_shot);
 
   void get_model_vector(double *out, size_t n);
   void set_model_vector(const double *in, size_t n);
@@ -139,7 +163,11 @@ class Model {
   void launch_velocity(double sdt);
   // variant 2: one fused launch per time step (fused.cuh)
   void fused_begin(int i_shot, int point_mode);
+  void fill_fused_model(int i_shot, void *out) const;
+  static void check_batch(Model *const *models, int n, int i_shot);
+  void adopt_batch_state(const Model &leader);
   int fused_auto_strip(int n_zwarps, int batch);
+  int pipe_warps() const;
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
   void win_geometry(int batch, int *tiles, int *strip);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
@@ -148,7 +176,14 @@ class Model {
   double *F(int k) const { return field_ptr(cur_, k); }  // current state: vx vz txx tzz txz
   void write_wavefield_files(int it);
 
-  Config cfg_;
+  Config cfg_;  // of a slab: nx is the LOCAL row count, source/receiver indices stay global
+  bool slab_ = false;
+  int x_off_ = 0, nx_global_ = 0, halo_lo_ = 0, halo_hi_ = 0;
+  DeviceBuffer halo_send_, halo_recv_;  // [lo | hi][5 fields][halo rows * ld]
+  struct March {
+    bool active = false, adjoint = false, store = false;
+    int i_shot = 0, it = 0;
+  } march_;
   int device_ = 0;
   cudaStream_t stream_ = nullptr;
   cudaEvent_t ev_begin_ = nullptr, ev_end_ = nullptr, ev_t0_ = nullptr, ev_t1_ = nullptr;
@@ -177,7 +212,8 @@ class Model {
   DeviceBuffer rec_index_, rec_next_, rec_heads_;
   int n_rec_heads_ = 0;
   DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_;  // receivers bucketed by grid row (fused.cuh)
-  DeviceBuffer fused_model_;                             // one FusedModel (device copy of the pointers)
+  DeviceBuffer fused_model_;                             // FusedModel per batch member (device copy of the pointers)
+  std::vector<Model *> batch_followers_;                 // non-empty only inside forward_batch / adjoint_batch
   std::vector<ShotPlan> plans_;
   std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
   std::vector<DeviceBuffer> snapshot_pool_;  // released buffers, reused by ensure_snapshots
@@ -192,7 +228,7 @@ class Model {
   int strip_ = 16, block_ = 128;
   int fused_strip_ = 0 /* 0 = whole waves */, fused_block_ = 128;
   int fused_resident_blocks_ = 0;
-  int pipe_stages_ = 4, pipe_warps_ = 8, pipe_resident_ = 0;
+  int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
   int win_config_ = 0, win_resident_ = 0;
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;

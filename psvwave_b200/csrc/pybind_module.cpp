@@ -271,9 +271,21 @@ class FdModel {
     return py::make_tuple((size_t)(uintptr_t)p, n);
   }
 
+  psv_handle handle() const { return h_; }
+
  private:
   psv_handle h_ = nullptr;
 };
+
+std::vector<psv_handle> batch_handles(const std::vector<FdModel *> &models) {
+  std::vector<psv_handle> h;
+  h.reserve(models.size());
+  for (const FdModel *m : models) {
+    if (!m) throw py::value_error("None in the list of models.");
+    h.push_back(m->handle());
+  }
+  return h;
+}
 
 }  // namespace
 
@@ -287,6 +299,23 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
   });
   m.def("max_variant", [] { return psv_variant_count() - 1; });
   m.def("version", [] { return std::string(psv_version()); });
+  // additive: Monte-Carlo ensembles, one launch per time step for all models (psv_forward_batch)
+  m.def(
+      "forward_batch",
+      [](const std::vector<FdModel *> &models, int i_shot, bool store_fields) {
+        const std::vector<psv_handle> h = batch_handles(models);
+        py::gil_scoped_release release;
+        check(psv_forward_batch(h.data(), (int)h.size(), i_shot, store_fields));
+      },
+      py::arg("models"), py::arg("i_shot"), py::arg("store_fields") = true);
+  m.def(
+      "adjoint_batch",
+      [](const std::vector<FdModel *> &models, int i_shot) {
+        const std::vector<psv_handle> h = batch_handles(models);
+        py::gil_scoped_release release;
+        check(psv_adjoint_batch(h.data(), (int)h.size(), i_shot));
+      },
+      py::arg("models"), py::arg("i_shot"));
 
 #define RO_INT(name, key) def_property_readonly(name, [](const FdModel &s) { return s.geti(key); })
 #define RO_REAL(name, key) def_property_readonly(name, [](const FdModel &s) { return s.getr(key); })
