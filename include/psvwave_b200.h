@@ -203,6 +203,32 @@ int psv_synchronize(psv_handle h);
  * those of handles[0].  Needs a fused variant (>= 2, the default). */
 int psv_forward_batch(const psv_handle *handles, int n, int i_shot, int store_fields);
 int psv_adjoint_batch(const psv_handle *handles, int n, int i_shot);
+/* ---- domain split for grids too large for one GPU (no counterpart in the reference) --
+ * The grid is cut into `nranks` x-slabs (rows are contiguous in z, so a halo is a block of whole
+ * rows).  A slab handle is an fdModel over the rows it owns plus `halo_rows` rows of each
+ * neighbour: grid arrays (get/set) have the LOCAL shape (nx_local, nz), sources/receivers/time
+ * axis/seismograms are those of the whole experiment.  One time step consumes 4 halo rows, so
+ * halo_rows = 4k lets k steps run between two exchanges.  The host layer drives all slabs in
+ * lock-step:   begin;  repeat { steps(k); pack; <swap send/recv buffers with the neighbours>;
+ * unpack; }  end;   seismograms are valid for receivers on owned rows, kernels on owned rows.
+ * psv_forward_simulate / psv_adjoint_simulate refuse a slab that has neighbours. */
+int psv_create_slab_from_ini(const char *ini_path, int rank, int nranks, int halo_rows, psv_handle *out);
+/* out[7] = nx_global, first global row (x offset), nx_local, halo rows below, halo rows above,
+ * row pitch in doubles, 1 if the handle is a slab */
+int psv_slab_info(psv_handle h, long long out[7]);
+int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields);
+/* Enqueue up to n time steps on the model's stream (no wait); *done = steps enqueued, 0 at the end. */
+int psv_march_steps(psv_handle h, int n, int *done);
+int psv_march_end(psv_handle h);
+/* Stage the owned edge rows of vx vz txx tzz txz into the send buffers / the received rows into
+ * the halo (stream-ordered kernels).  Buffers: [5 fields][halo_rows * pitch] doubles per side,
+ * `count` doubles each; a side without neighbour has NULL pointers. */
+int psv_halo_pack(psv_handle h);
+int psv_halo_unpack(psv_handle h);
+int psv_halo_buffers(psv_handle h, void **send_lo, void **send_hi, void **recv_lo, void **recv_hi,
+                     size_t *count);
+/* The CUDA stream (cudaStream_t) every kernel and copy of this model is ordered on. */
+int psv_stream(psv_handle h, void **stream);
 /* Device stopwatch on the model's stream (CUDA events): start records an event, stop records a
  * second one, waits for it and returns the milliseconds between the two. */
 int psv_timer_start(psv_handle h);

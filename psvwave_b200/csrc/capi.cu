@@ -390,6 +390,50 @@ int psv_adjoint_batch(const psv_handle *handles, int n, int i_shot) {
   });
 }
 
+int psv_create_slab_from_ini(const char *ini_path, int rank, int nranks, int halo_rows, psv_handle *out) {
+  return guarded([&] {
+    if (!ini_path || !out) throw psv::invalid_argument("Null argument.");
+    *out = nullptr;
+    psv::Config cfg = psv::config_from_ini(ini_path);
+    const psv::SlabSpec slab = psv::slab_partition(cfg.nx, rank, nranks, halo_rows);
+    const int dev = pick_device();
+    *out = new psv_model{new psv::Model(std::move(cfg), dev, &slab)};
+  });
+}
+int psv_slab_info(psv_handle h, long long out[7]) {
+  return guarded([&] { model(h).slab_info(out); });
+}
+int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields) {
+  return guarded([&] { model(h).march_begin(i_shot, adjoint != 0, store_fields != 0); });
+}
+int psv_march_steps(psv_handle h, int n, int *done) {
+  return guarded([&] {
+    const int d = model(h).march_steps(n);
+    if (done) *done = d;
+  });
+}
+int psv_march_end(psv_handle h) {
+  return guarded([&] { model(h).march_end(); });
+}
+int psv_halo_pack(psv_handle h) {
+  return guarded([&] { model(h).halo_pack(); });
+}
+int psv_halo_unpack(psv_handle h) {
+  return guarded([&] { model(h).halo_unpack(); });
+}
+int psv_halo_buffers(psv_handle h, void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) {
+  return guarded([&] {
+    if (!send_lo || !send_hi || !recv_lo || !recv_hi || !count) throw psv::invalid_argument("Null argument.");
+    model(h).halo_buffers(send_lo, send_hi, recv_lo, recv_hi, count);
+  });
+}
+int psv_stream(psv_handle h, void **stream) {
+  return guarded([&] {
+    if (!stream) throw psv::invalid_argument("Null argument.");
+    *stream = (void *)model(h).stream();
+  });
+}
+
 int psv_release_snapshots(psv_handle h, int i_shot) {
   return guarded([&] { model(h).release_snapshots(i_shot); });
 }

@@ -56,7 +56,33 @@ std::string zero_pad(int v, int width) {
 // ---------------------------------------------------------------------------------------------
 // construction
 // ---------------------------------------------------------------------------------------------
-Model::Model(Config cfg, int device) : cfg_(std::move(cfg)), device_(device) {
+SlabSpec slab_partition(int nx_global, int rank, int nranks, int halo) {
+  if (nranks < 1 || rank < 0 || rank >= nranks) throw invalid_argument("Slab rank out of range.");
+  if (halo < 4 || halo % 4 != 0)
+    throw invalid_argument("The halo must be a positive multiple of 4 rows (one time step consumes 4).");
+  const int base = nx_global / nranks, rem = nx_global % nranks;
+  const int own0 = rank * base + std::min(rank, rem), own1 = own0 + base + (rank < rem ? 1 : 0);
+  if (nranks > 1 && own1 - own0 < halo)
+    throw invalid_argument("Too many slabs: every slab must own at least `halo` rows.");
+  SlabSpec s;
+  s.halo_lo = rank > 0 ? halo : 0;
+  s.halo_hi = rank < nranks - 1 ? halo : 0;
+  s.x0 = own0 - s.halo_lo;
+  s.x1 = own1 + s.halo_hi;
+  return s;
+}
+
+Model::Model(Config cfg, int device, const SlabSpec *slab) : cfg_(std::move(cfg)), device_(device) {
+  nx_global_ = cfg_.nx;
+  if (slab) {
+    if (slab->x0 < 0 || slab->x1 > cfg_.nx || slab->x1 - slab->x0 < slab->halo_lo + slab->halo_hi + 1)
+      throw invalid_argument("Slab rows out of range.");
+    slab_ = true;
+    x_off_ = slab->x0;
+    halo_lo_ = slab->halo_lo;
+    halo_hi_ = slab->halo_hi;
+    cfg_.nx = slab->x1 - slab->x0;  // everything below sizes by the local row count
+  }
   bind();
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
@@ -66,6 +92,11 @@ Model::Model(Config cfg, int device) : cfg_(std::move(cfg)), device_(device) {
   allocate();
   initialize_host_tables();
   build_plans();
+  if (slab_) {
+    const size_t bytes = 2 * 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_ * sizeof(double);
+    halo_send_.allocate(bytes);
+    halo_recv_.allocate(bytes);
+  }
   PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
@@ -162,8 +193,13 @@ void Model::build_plans() {
   // receivers: linear index + chains of receivers sharing a grid point
   std::vector<int> idx(std::max(c.nr, 1), 0), next(std::max(c.nr, 1), -1), heads;
   std::map<int, int> last;
+  // rows of a slab: global row - x_off_; points outside the slab take no part (local row -1)
+  auto local_row = [&](int gx) {
+    const int x = gx - x_off_;
+    return x >= 0 && x < c.nx ? x : -1;
+  };
   for (int r = 0; r < c.nr; ++r) {
-    idx[r] = c.ix_receivers[r] * ld_ + c.iz_receivers[r];
+    idx[r] = std::max(local_row(c.ix_receivers[r]), 0) * ld_ + c.iz_receivers[r];  // (variants 0/1: whole grids only)
     auto it = last.find(idx[r]);
     if (it == last.end()) heads.push_back(r);
     else next[it->second] = r;
@@ -181,13 +217,14 @@ void Model::build_plans() {
   // receivers bucketed by grid row for the fused step kernel: stable sort by ix keeps the
   // receiver order inside a row (adjoint injection at coinciding receivers is order-sensitive)
   {
-    std::vector<int> order(c.nr), row_start(c.nx + 1, 0), rz(std::max(c.nr, 1), 0), rid(std::max(c.nr, 1), 0);
-    for (int r = 0; r < c.nr; ++r) order[r] = r;
+    std::vector<int> order, row_start(c.nx + 1, 0), rz(std::max(c.nr, 1), 0), rid(std::max(c.nr, 1), 0);
+    for (int r = 0; r < c.nr; ++r)
+      if (local_row(c.ix_receivers[r]) >= 0) order.push_back(r);
     std::stable_sort(order.begin(), order.end(),
                      [&](int a, int b) { return c.ix_receivers[a] < c.ix_receivers[b]; });
-    for (int r = 0; r < c.nr; ++r) ++row_start[c.ix_receivers[r] + 1];
+    for (int r : order) ++row_start[local_row(c.ix_receivers[r]) + 1];
     for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
-    for (int q = 0; q < c.nr; ++q) {
+    for (size_t q = 0; q < order.size(); ++q) {
       rz[q] = c.iz_receivers[order[q]];
       rid[q] = order[q];
     }
@@ -205,7 +242,9 @@ void Model::build_plans() {
     std::vector<InjectOp> ops;
     std::vector<int> op_heads;
     std::map<std::pair<int, int>, int> last_op;
-    auto push = [&](int field, int x, int z, int source, double weight, double sign, double d4) {
+    auto push = [&](int field, int gx, int z, int source, double weight, double sign, double d4) {
+      const int x = local_row(gx);
+      if (x < 0) return;  // target row belongs to another slab
       InjectOp op;
       op.point = x * ld_ + z;
       op.field = field;
@@ -273,7 +312,16 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   PSV_CUDA(cudaEventCreate(&ev_end_));
   PSV_CUDA(cudaEventCreate(&ev_t0_));
   PSV_CUDA(cudaEventCreate(&ev_t1_));
+  slab_ = o.slab_;
+  x_off_ = o.x_off_;
+  nx_global_ = o.nx_global_;
+  halo_lo_ = o.halo_lo_;
+  halo_hi_ = o.halo_hi_;
   allocate();
+  if (slab_) {
+    halo_send_.allocate(o.halo_send_.bytes());
+    halo_recv_.allocate(o.halo_recv_.bytes());
+  }
   t_host_ = o.t_host_;
   stf_host_ = o.stf_host_;
   moment_host_ = o.moment_host_;
@@ -451,7 +499,7 @@ void launch_velocity_t(int variant, const VelocityArgs &a, int block, cudaStream
 void Model::launch_stress(double sdt, int mode, int i_shot, int snap) {
   const Config &c = cfg_;
   StressArgs a{};
-  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, 0, c.nx};
   a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
   a.vx = F(0);
   a.vz = F(1);
@@ -487,7 +535,7 @@ void Model::launch_stress(double sdt, int mode, int i_shot, int snap) {
 void Model::launch_velocity(double sdt) {
   const Config &c = cfg_;
   VelocityArgs a{};
-  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  a.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, 0, c.nx};
   a.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
   a.txx = F(2);
   a.tzz = F(3);
@@ -789,8 +837,10 @@ void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, si
 
 void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
   const Config &c = cfg_;
+  if (slab_ && variant_ != 2 && variant_ != 3)
+    throw invalid_argument("A slab of a split grid runs the fused variants 2 and 3 only.");
   FusedCommon fc{};
-  fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary};
+  fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, x_off_, nx_global_};
   fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
   fc.taper_table = taper_table_.as<>();
   fc.parity = cur_;
@@ -801,8 +851,9 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.it_step = 0;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
-  fc.wx0 = c.np_boundary + c.nx_inner_boundary;
-  fc.wx1 = c.np_boundary + c.nx_inner - c.nx_inner_boundary;
+  // free window in local rows; a slab correlates only on the rows it owns
+  fc.wx0 = std::max(c.np_boundary + c.nx_inner_boundary - x_off_, halo_lo_);
+  fc.wx1 = std::min(c.np_boundary + c.nx_inner - c.nx_inner_boundary - x_off_, c.nx - halo_hi_);
   fc.wz0 = c.np_boundary + c.nz_inner_boundary;
   fc.wz1 = c.np_boundary + c.nz_inner - c.nz_inner_boundary;
   fc.sidt = c.snapshot_interval * c.dt;
@@ -911,6 +962,9 @@ struct Profiler {  // CUDA events around sampled sweep launches
 // fdModel::forward_simulate (src/fdModel.cpp:526-787)
 void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool output_wavefields) {
   check_shot(i_shot);
+  if (slab_ && (halo_lo_ || halo_hi_))
+    throw state_error("This model is one slab of a split grid: drive it with psv_march_* and exchange halos "
+                      "(psvwave_b200.SlabDomain does).");
   bind();
   const Config &c = cfg_;
   if (store_fields) ensure_snapshots(i_shot);
@@ -992,6 +1046,9 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
 // fdModel::adjoint_simulate (src/fdModel.cpp:789-969)
 void Model::adjoint_simulate(int i_shot, bool verbose) {
   check_shot(i_shot);
+  if (slab_ && (halo_lo_ || halo_hi_))
+    throw state_error("This model is one slab of a split grid: drive it with psv_march_* and exchange halos "
+                      "(psvwave_b200.SlabDomain does).");
   bind();
   const Config &c = cfg_;
   if (snapshots_[i_shot].empty())
@@ -1051,6 +1108,134 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
     std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
   }
+}
+
+// ---- domain split: the time loop in pieces + halo staging (SURVEY 8e "large single grids") ----
+// One fused step consumes 4 halo rows (new velocities of row x need the old state of rows x-4..x+4),
+// so a halo of H rows lets H/4 steps run between two exchanges; the rows a step invalidates lie in
+// the halo and are overwritten by the next exchange.  Snapshots, correlation and receiver samples
+// are pointwise on rows the slab owns, which are always valid.
+void Model::march_begin(int i_shot, bool adjoint, bool store_fields) {
+  check_shot(i_shot);
+  bind();
+  if (variant_ != 2 && variant_ != 3) throw invalid_argument("psv_march_* needs the fused variant 2 or 3.");
+  if (march_.active) throw state_error("A march is already in progress on this model.");
+  if (adjoint && snapshots_[i_shot].empty())
+    throw state_error("The adjoint march needs the forward wavefield of this shot: run the stored forward march first.");
+  if (!adjoint && store_fields) ensure_snapshots(i_shot);
+  stat_launches_ = 0;
+  stat_pair_launches_ = 0;
+  zero_dynamic_fields();
+  PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+  fused_begin(i_shot, adjoint ? POINT_ADJOINT : POINT_FORWARD);
+  march_.active = true;
+  march_.adjoint = adjoint;
+  march_.store = store_fields;
+  march_.i_shot = i_shot;
+  march_.it = adjoint ? cfg_.nt - 1 : 0;
+}
+
+int Model::march_steps(int n) {
+  if (!march_.active) throw state_error("psv_march_steps without psv_march_begin.");
+  bind();
+  const Config &c = cfg_;
+  int done = 0;
+  for (; done < n; ++done) {
+    const int it = march_.it;
+    if (march_.adjoint) {
+      if (it < 0) break;
+      const bool corr = it % c.snapshot_interval == 0;
+      launch_fused(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, c.nr > 0 ? POINT_ADJOINT : POINT_NONE, march_.i_shot,
+                   it / c.snapshot_interval, it, 0);
+      --march_.it;
+    } else {
+      if (it >= c.nt) break;
+      const bool snap = march_.store && it % c.snapshot_interval == 0;
+      launch_fused(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, POINT_FORWARD, march_.i_shot, it / c.snapshot_interval,
+                   it, 0);
+      ++march_.it;
+    }
+  }
+  PSV_CUDA(cudaGetLastError());
+  return done;
+}
+
+void Model::march_end() {
+  if (!march_.active) throw state_error("psv_march_end without psv_march_begin.");
+  bind();
+  march_.active = false;
+  PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  float ms = 0;
+  PSV_CUDA(cudaEventElapsedTime(&ms, ev_begin_, ev_end_));
+  stat_elapsed_ms_ = ms;
+}
+
+namespace {
+// rows [row0, row0 + rows) of the 5 state arrays <-> one contiguous staging block per side
+struct HaloArgs {
+  double *state;  // vx of the current buffer; field k at + k * field_stride
+  size_t field_stride;
+  double *staging;  // [side][field][chunk]
+  size_t chunk;     // rows * ld
+  size_t row_off[2];  // first element of the rows of side 0 / 1 inside a field
+  int active[2];
+};
+template <bool PACK>
+__global__ void halo_copy_kernel(const HaloArgs a) {
+  const int side = blockIdx.y / 5, field = blockIdx.y % 5;
+  if (!a.active[side]) return;
+  double2 *grid = reinterpret_cast<double2 *>(a.state + field * a.field_stride + a.row_off[side]);
+  double2 *stage = reinterpret_cast<double2 *>(a.staging + ((size_t)side * 5 + field) * a.chunk);
+  const size_t n2 = a.chunk >> 1;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) {
+    if (PACK) stage[i] = grid[i];
+    else grid[i] = stage[i];
+  }
+}
+}  // namespace
+
+void Model::halo_pack() {
+  if (!slab_) throw state_error("Not a slab of a split grid.");
+  bind();
+  const int H = std::max(halo_lo_, halo_hi_);
+  if (H == 0) return;
+  HaloArgs a{F(0), field_stride_, halo_send_.as<>(), (size_t)H * ld_,
+             {(size_t)halo_lo_ * ld_, (size_t)(cfg_.nx - halo_hi_ - H) * ld_}, {halo_lo_ > 0, halo_hi_ > 0}};
+  halo_copy_kernel<true><<<dim3(64, 10), 256, 0, stream_>>>(a);
+  PSV_CUDA(cudaGetLastError());
+  ++stat_launches_;
+}
+
+void Model::halo_unpack() {
+  if (!slab_) throw state_error("Not a slab of a split grid.");
+  bind();
+  const int H = std::max(halo_lo_, halo_hi_);
+  if (H == 0) return;
+  HaloArgs a{F(0), field_stride_, halo_recv_.as<>(), (size_t)H * ld_,
+             {(size_t)0, (size_t)(cfg_.nx - H) * ld_}, {halo_lo_ > 0, halo_hi_ > 0}};
+  halo_copy_kernel<false><<<dim3(64, 10), 256, 0, stream_>>>(a);
+  PSV_CUDA(cudaGetLastError());
+  ++stat_launches_;
+}
+
+void Model::halo_buffers(void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) const {
+  const size_t side = 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_;
+  *send_lo = halo_lo_ ? halo_send_.as<>() : nullptr;
+  *send_hi = halo_hi_ ? halo_send_.as<>() + side : nullptr;
+  *recv_lo = halo_lo_ ? halo_recv_.as<>() : nullptr;
+  *recv_hi = halo_hi_ ? halo_recv_.as<>() + side : nullptr;
+  *count = side;
+}
+
+void Model::slab_info(long long out[7]) const {
+  out[0] = nx_global_;
+  out[1] = x_off_;
+  out[2] = cfg_.nx;
+  out[3] = halo_lo_;
+  out[4] = halo_hi_;
+  out[5] = ld_;
+  out[6] = slab_ ? 1 : 0;
 }
 
 // ---- Monte-Carlo ensembles: n models of one experiment, one launch per time step ---------------
@@ -1233,6 +1418,7 @@ VectorArgs vector_args(const Config &c, int ld) {
 
 void Model::get_model_vector(double *out, size_t n) {
   bind();
+  if (slab_) throw state_error("Model and gradient vectors span the whole grid: assemble them from the slabs (psvwave_b200.SlabDomain does).");
   if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Model vector has the wrong length.");
   const VectorArgs a = vector_args(cfg_, ld_);
   if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
@@ -1245,6 +1431,7 @@ void Model::get_model_vector(double *out, size_t n) {
 
 void Model::set_model_vector(const double *in, size_t n) {
   bind();
+  if (slab_) throw state_error("Model and gradient vectors span the whole grid: assemble them from the slabs (psvwave_b200.SlabDomain does).");
   if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Model vector has the wrong length.");
   const VectorArgs a = vector_args(cfg_, ld_);
   if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
@@ -1257,6 +1444,7 @@ void Model::set_model_vector(const double *in, size_t n) {
 
 void Model::get_gradient_vector(double *out, size_t n) {
   bind();
+  if (slab_) throw state_error("Model and gradient vectors span the whole grid: assemble them from the slabs (psvwave_b200.SlabDomain does).");
   if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Gradient vector has the wrong length.");
   const VectorArgs a = vector_args(cfg_, ld_);
   if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
@@ -1318,7 +1506,8 @@ void Model::get_array(psv_array which, double *out, size_t count) {
     case PSV_TAPER: {
       for (int ix = 0; ix < c.nx; ++ix)
         for (int iz = 0; iz < c.nz; ++iz) {
-          const int d = std::min(std::min(ix, c.nx - 1 - ix), std::min(iz, c.nz - 1 - iz)) + 1;
+          const int gx = ix + x_off_;
+          const int d = std::min(std::min(gx, nx_global_ - 1 - gx), std::min(iz, c.nz - 1 - iz)) + 1;
           out[(size_t)ix * c.nz + iz] = taper_host_[std::min(d, c.np_boundary)];
         }
       return;

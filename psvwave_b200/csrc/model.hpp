@@ -76,7 +76,7 @@ SlabSpec slab_partition(int nx_global, int rank, int nranks, int halo);
 class Model {
  public:
   static constexpr int kVariantCount = 6;
-  explicit Model(Config cfg, int device);
+  explicit Model(Config cfg, int device, const SlabSpec *slab = nullptr);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
 

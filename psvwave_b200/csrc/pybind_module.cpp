@@ -273,6 +273,52 @@ class FdModel {
 
   psv_handle handle() const { return h_; }
 
+  // domain split (psv_create_slab_from_ini ... psv_stream)
+  static FdModel *slab(const std::string &path, int rank, int nranks, int halo_rows) {
+    psv_handle h = nullptr;
+    check(psv_create_slab_from_ini(path.c_str(), rank, nranks, halo_rows, &h));
+    return new FdModel(h);
+  }
+  py::dict slab_info() const {
+    long long v[7];
+    check(psv_slab_info(h_, v));
+    py::dict d;
+    d["nx_global"] = v[0];
+    d["x_offset"] = v[1];
+    d["nx_local"] = v[2];
+    d["halo_lo"] = v[3];
+    d["halo_hi"] = v[4];
+    d["pitch"] = v[5];
+    d["is_slab"] = v[6] != 0;
+    return d;
+  }
+  void march_begin(int i_shot, bool adjoint, bool store_fields) {
+    check(psv_march_begin(h_, i_shot, adjoint, store_fields));
+  }
+  int march_steps(int n) {
+    int done = 0;
+    check(psv_march_steps(h_, n, &done));
+    return done;
+  }
+  void march_end() {
+    py::gil_scoped_release release;
+    check(psv_march_end(h_));
+  }
+  void halo_pack() { check(psv_halo_pack(h_)); }
+  void halo_unpack() { check(psv_halo_unpack(h_)); }
+  py::tuple halo_buffers() const {
+    void *p[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t n = 0;
+    check(psv_halo_buffers(h_, &p[0], &p[1], &p[2], &p[3], &n));
+    return py::make_tuple((size_t)(uintptr_t)p[0], (size_t)(uintptr_t)p[1], (size_t)(uintptr_t)p[2],
+                          (size_t)(uintptr_t)p[3], n);
+  }
+  size_t stream() const {
+    void *s = nullptr;
+    check(psv_stream(h_, &s));
+    return (size_t)(uintptr_t)s;
+  }
+
  private:
   psv_handle h_ = nullptr;
 };
@@ -374,6 +420,8 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       // additive (not bound by the reference)
       .RO_INT("nr", PSV_INT_NR)
       .RO_INT("device", PSV_INT_DEVICE)
+      .RO_INT("basis_gridpoints_x", PSV_INT_BASIS_GRIDPOINTS_X)
+      .RO_INT("basis_gridpoints_z", PSV_INT_BASIS_GRIDPOINTS_Z)
       .def("run_model", &FdModel::run_model, py::arg("verbose") = false, py::arg("simulate_adjoint") = true)
       .def("write_receivers", &FdModel::write_receivers)
       .def("load_receivers", &FdModel::load_receivers, py::arg("verbose") = false)
@@ -391,5 +439,15 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       .def("_timer_start", &FdModel::timer_start)
       .def("_timer_stop", &FdModel::timer_stop)
       .def("synchronize", &FdModel::synchronize)
-      .def("_device_kernel_buffer", &FdModel::device_kernel_buffer);
+      .def("_device_kernel_buffer", &FdModel::device_kernel_buffer)
+      .def_static("_slab", &FdModel::slab, py::return_value_policy::take_ownership, py::arg("path"), py::arg("rank"),
+                  py::arg("nranks"), py::arg("halo_rows"))
+      .def("_slab_info", &FdModel::slab_info)
+      .def("_march_begin", &FdModel::march_begin)
+      .def("_march_steps", &FdModel::march_steps)
+      .def("_march_end", &FdModel::march_end)
+      .def("_halo_pack", &FdModel::halo_pack)
+      .def("_halo_unpack", &FdModel::halo_unpack)
+      .def("_halo_buffers", &FdModel::halo_buffers)
+      .def("_stream", &FdModel::stream);
 }
