@@ -194,6 +194,22 @@ int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out);
  * used by the host layer for the cross-rank sum (one all-reduce) over NCCL. */
 int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count);
 int psv_synchronize(psv_handle h);
+/* Gradient of all shots, one shot at a time: forward(store) -> misfit of the shot ->
+ * adjoint sources -> adjoint (-> psv_release_snapshots of that shot if release_each_shot), then
+ * psv_map_kernels_to_velocity.  Same result as psv_run_model(h, 0, 1) (src/fdModel.cpp:1291-1308)
+ * with one shot's snapshots resident instead of all; *misfit_out = sum of the per-shot misfits. */
+int psv_run_gradient(psv_handle h, int release_each_shot, double *misfit_out);
+/* Device-resident steepest descent (the loop of the reference's
+ * tests/python/test_descent.py:106-129): model vector <- model vector - step_length * gradient
+ * vector on the free-window basis, then update_from_velocity; bit-identical to
+ * get_model_vector / get_gradient_vector / set_model_vector on the host.  psv_gradient_descent reads
+ * the model vector ONCE into device memory and then runs `iterations` rounds of { m -= step * g;
+ * set_model_vector(m); psv_run_gradient } like the reference loop (which never re-reads m), reporting
+ * the misfit after each round (misfits_out may be NULL); the kernels of the starting model must
+ * exist (psv_run_gradient). */
+int psv_descent_step(psv_handle h, double step_length);
+int psv_gradient_descent(psv_handle h, int iterations, double step_length, int release_each_shot,
+                         double *misfits_out);
 /* Monte-Carlo ensembles (SURVEY 8e "replicas only"; the reference's route is n independent copies of
  * the object, src/fdModel.cpp:64-97, each simulated on its own).  The n models must describe one
  * experiment on one device (same grid, time axis, boundary, sources, receivers, snapshot interval);

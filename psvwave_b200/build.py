@@ -48,6 +48,7 @@ def build(force: bool = False, verbose: bool = False) -> None:
         cmd = [NVCC, "-ccbin", HOST_CXX, "-std=c++17", "-O3", "-lineinfo", *ARCH,
                "-Xcompiler", "-fPIC,-O3,-Wall,-ffp-contract=off",
                "-Xptxas", "-v" if verbose else "-O3",
+               *os.environ.get("PSV_EXTRA_NVCC_FLAGS", "").split(),
                "--shared", "-cudart", "static", "-I", INCLUDE, "-o", LIB,
                *[os.path.join(CSRC, f) for f in LIB_SOURCES]]
         _run(cmd, verbose)

@@ -367,6 +367,20 @@ int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, si
   return guarded([&] { model(h).load_vector(path, verbose != 0, out, n); });
 }
 
+int psv_run_gradient(psv_handle h, int release_each_shot, double *misfit_out) {
+  return guarded([&] {
+    const double m = model(h).run_gradient(release_each_shot != 0);
+    if (misfit_out) *misfit_out = m;
+  });
+}
+int psv_descent_step(psv_handle h, double step_length) {
+  return guarded([&] { model(h).descent_step(step_length); });
+}
+int psv_gradient_descent(psv_handle h, int iterations, double step_length, int release_each_shot,
+                         double *misfits_out) {
+  return guarded([&] { model(h).gradient_descent(iterations, step_length, release_each_shot != 0, misfits_out); });
+}
+
 namespace {
 std::vector<psv::Model *> batch_models(const psv_handle *handles, int n) {
   if (!handles || n < 1) throw psv::invalid_argument("Batched simulate needs at least one model.");

@@ -1335,6 +1335,72 @@ void Model::run_model(bool verbose, bool simulate_adjoint) {
 // ---------------------------------------------------------------------------------------------
 // point-wise stages
 // ---------------------------------------------------------------------------------------------
+namespace {
+VectorArgs vector_args(const Config &c, int ld);
+}  // namespace
+
+// Per-shot gradient loop: forward(store) -> misfit of the shot -> adjoint sources ->
+// adjoint -> (drop the shot's snapshots), then the map.  Same kernels and accumulation order across
+// shots as run_model (src/fdModel.cpp:1291-1308), but only ONE shot's snapshots are resident at a
+// time.  The misfit is the sum of the per-shot misfits (the reference sums shot-major as well).
+double Model::run_gradient(bool release_each_shot) {
+  reset_kernels();
+  double total = 0.0;
+  for (int s = 0; s < cfg_.n_shots; ++s) {
+    forward_simulate(s, true, false, false);
+    total += calculate_l2_misfit_shot(s);
+    calculate_l2_adjoint_sources();
+    adjoint_simulate(s, false);
+    if (release_each_shot) release_snapshots(s);
+  }
+  map_kernels_to_velocity();
+  misfit_ = total;
+  return total;
+}
+
+// Device-resident steepest descent (tests/python/test_descent.py:95-129 of the
+// reference): m = get_model_vector() once, then per round  g = get_gradient_vector();  m -= step * g;
+// set_model_vector(m)  -- all three on the device, m and g never visit the host.
+void Model::descent_load() {  // m <- block means of (vp, vs, rho)
+  bind();
+  if (slab_) throw state_error("Model vectors span the whole grid: not available on a slab.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  const size_t n = (size_t)cfg_.free_parameters;
+  if (descent_vec_.bytes() < 2 * n * sizeof(double)) descent_vec_.allocate(2 * n * sizeof(double));
+  vector_kernel<VEC_MEAN><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(),
+                                                                       descent_vec_.as<>());
+  PSV_CUDA(cudaGetLastError());
+}
+
+void Model::descent_apply(double step) {  // g <- block sums of the kernels; m -= step * g; fields <- m
+  const VectorArgs a = vector_args(cfg_, ld_);
+  const size_t n = (size_t)cfg_.free_parameters;
+  double *m = descent_vec_.as<>(), *g = m + n;
+  vector_kernel<VEC_SUM><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_kernel_.data(), vs_kernel_.data(),
+                                                                      density_v_kernel_.data(), g);
+  descent_axpy_kernel<<<blocks_for(n, 256), 256, 0, stream_>>>(m, g, step, n);
+  vector_kernel<VEC_FILL><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(), m);
+  PSV_CUDA(cudaGetLastError());
+  update_from_velocity();  // src/fdModel.cpp:1456
+}
+
+void Model::descent_step(double step) {
+  descent_load();
+  descent_apply(step);
+}
+
+// `iterations` rounds of { m -= step * g; set; gradient of all shots } without leaving the device;
+// the kernels of the current model must exist (run_model / run_gradient) before the first round.
+void Model::gradient_descent(int iterations, double step, bool release_each_shot, double *misfits) {
+  if (iterations < 0) throw invalid_argument("iterations must be >= 0");
+  descent_load();
+  for (int i = 0; i < iterations; ++i) {
+    descent_apply(step);
+    const double m = run_gradient(release_each_shot);
+    if (misfits) misfits[i] = m;
+  }
+}
+
 void Model::update_from_velocity() {
   bind();
   update_from_velocity_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(

@@ -93,6 +93,11 @@ class Model {
   void map_kernels_to_velocity();
   void update_from_velocity();
   void run_model(bool verbose, bool simulate_adjoint);
+  double run_gradient(bool release_each_shot);
+  void descent_step(double step);
+  void descent_load();
+  void descent_apply(double step);
+  void gradient_descent(int iterations, double step, bool release_each_shot, double *misfits);
   // Monte-Carlo ensembles (SURVEY 8e "replicas only", config C4): n models that share one
   // experiment (grid, time axis, sources, receivers) advance together, ONE launch per time step
   // for the whole ensemble (blockIdx.z = model).  Each model keeps its own medium, fields,
@@ -217,6 +222,7 @@ class Model {
   std::vector<ShotPlan> plans_;
   std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
   std::vector<DeviceBuffer> snapshot_pool_;  // released buffers, reused by ensure_snapshots
+  DeviceBuffer descent_vec_;             // [model vector | gradient vector] of the device-resident descent
   DeviceBuffer scratch_;                 // reduction partials / vectors
 
   double misfit_ = 0.0;

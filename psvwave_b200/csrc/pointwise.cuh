@@ -221,4 +221,12 @@ __global__ void vector_kernel(const VectorArgs a, double *f0, double *f1, double
   }
 }
 
+// Steepest-descent update of a device-resident model vector: m[k] <- m[k] - step * g[k], the
+// `m -= step * g` of the reference's tests/python/test_descent.py:110 with explicitly rounded
+// operations (no FMA), so the device loop is bit-identical to the host loop.
+__global__ void descent_axpy_kernel(double *m, const double *g, const double step, const size_t n) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) m[k] = __dsub_rn(m[k], __dmul_rn(step, g[k]));
+}
+
 }  // namespace psv

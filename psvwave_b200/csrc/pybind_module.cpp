@@ -230,6 +230,22 @@ class FdModel {
     py::gil_scoped_release release;
     check(psv_run_model(h_, verbose, simulate_adjoint));
   }
+  double run_gradient(bool release_each_shot) {
+    double m = 0;
+    py::gil_scoped_release release;
+    check(psv_run_gradient(h_, release_each_shot, &m));
+    return m;
+  }
+  void descent_step(double step) { check(psv_descent_step(h_, step)); }
+  py::array_t<double> gradient_descent(int iterations, double step, bool release_each_shot) {
+    if (iterations < 0) throw py::value_error("iterations must be >= 0");
+    py::array_t<double> misfits((py::ssize_t)iterations);
+    {
+      py::gil_scoped_release release;
+      check(psv_gradient_descent(h_, iterations, step, release_each_shot, misfits.mutable_data()));
+    }
+    return misfits;
+  }
   void write_receivers() { check(psv_write_receivers(h_)); }
   void load_receivers(bool verbose) { check(psv_load_receivers(h_, verbose)); }
   void write_sources() { check(psv_write_sources(h_)); }
@@ -423,6 +439,10 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       .RO_INT("basis_gridpoints_x", PSV_INT_BASIS_GRIDPOINTS_X)
       .RO_INT("basis_gridpoints_z", PSV_INT_BASIS_GRIDPOINTS_Z)
       .def("run_model", &FdModel::run_model, py::arg("verbose") = false, py::arg("simulate_adjoint") = true)
+      .def("run_gradient", &FdModel::run_gradient, py::arg("release_each_shot") = true)
+      .def("descent_step", &FdModel::descent_step, py::arg("step_length"))
+      .def("gradient_descent", &FdModel::gradient_descent, py::arg("iterations"), py::arg("step_length"),
+           py::arg("release_each_shot") = true)
       .def("write_receivers", &FdModel::write_receivers)
       .def("load_receivers", &FdModel::load_receivers, py::arg("verbose") = false)
       .def("write_sources", &FdModel::write_sources)

@@ -32,7 +32,7 @@ class SlabDomain:
 
     def __init__(self, ini: str, n_slabs: Optional[int] = None, halo_steps: int = 4, group=None,
                  rank: Optional[int] = None, world_size: Optional[int] = None, options: Optional[dict] = None,
-                 slab_factory=None):
+                 slab_factory=None, async_exchange: bool = True):
         if rank is None or world_size is None:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
@@ -41,6 +41,8 @@ class SlabDomain:
                 rank, world_size = 0, 1
         self.group, self.rank, self.world_size = group, int(rank), int(world_size)
         self.halo_rows = 4 * int(halo_steps)
+        self.async_exchange = bool(async_exchange)
+        self._views_cache = None
         if slab_factory is None:
             from . import fdModel
             slab_factory = fdModel._slab
@@ -168,21 +170,27 @@ class SlabDomain:
         import torch
         for m in self.slabs:
             m._halo_pack()
+        if self.world_size > 1 and self._stream_ordered():
+            # NCCL transport, no host synchronisation: the sends/receives are ordered after the pack and
+            # before the unpack through the model's own stream (torch sees it as an external stream)
+            import torch.distributed as dist
+            m = self.slabs[0]
+            if self._views_cache is None:
+                dev = torch.device("cuda", int(m.device))
+                self._views_cache = (self._views(m), torch.cuda.ExternalStream(m._stream(), device=dev))
+            (s_lo, s_hi, r_lo, r_hi), stream = self._views_cache
+            with torch.cuda.stream(stream):
+                for req in dist.batch_isend_irecv(self._p2p_ops(s_lo, s_hi, r_lo, r_hi)):
+                    req.wait()  # stream-side wait, the host runs on
+            m._halo_unpack()
+            return
         for m in self.slabs:
-            m.synchronize()  # staging buffers complete before another stream / NCCL reads them
+            m.synchronize()  # staging buffers complete before another stream / process reads them
         views = [self._views(m) for m in self.slabs]
-        cuda = views[0][0] is not None and views[0][0].is_cuda or views[0][1] is not None and views[0][1].is_cuda
+        cuda = any(v is not None and v.is_cuda for v in views[0])
         if self.world_size > 1:
             import torch.distributed as dist
-            s_lo, s_hi, r_lo, r_hi = views[0]
-            ops = []
-            if s_lo is not None:
-                ops += [dist.P2POp(dist.isend, s_lo, self.rank - 1, self.group),
-                        dist.P2POp(dist.irecv, r_lo, self.rank - 1, self.group)]
-            if s_hi is not None:
-                ops += [dist.P2POp(dist.isend, s_hi, self.rank + 1, self.group),
-                        dist.P2POp(dist.irecv, r_hi, self.rank + 1, self.group)]
-            for req in dist.batch_isend_irecv(ops):
+            for req in dist.batch_isend_irecv(self._p2p_ops(*views[0])):
                 req.wait()
         else:
             for k in range(len(self.slabs) - 1):
@@ -193,6 +201,22 @@ class SlabDomain:
             torch.cuda.current_stream().synchronize()
         for m in self.slabs:
             m._halo_unpack()
+
+    def _stream_ordered(self) -> bool:
+        import torch.distributed as dist
+        return (self.async_exchange and hasattr(self.slabs[0], "_stream")
+                and dist.get_backend(self.group) == "nccl")
+
+    def _p2p_ops(self, s_lo, s_hi, r_lo, r_hi):
+        import torch.distributed as dist
+        ops = []
+        if s_lo is not None:
+            ops += [dist.P2POp(dist.isend, s_lo, self.rank - 1, self.group),
+                    dist.P2POp(dist.irecv, r_lo, self.rank - 1, self.group)]
+        if s_hi is not None:
+            ops += [dist.P2POp(dist.isend, s_hi, self.rank + 1, self.group),
+                    dist.P2POp(dist.irecv, r_hi, self.rank + 1, self.group)]
+        return ops
 
     # ---- assembling whole-grid results --------------------------------------------------------
     def _sum_over_ranks(self, a: np.ndarray) -> np.ndarray:

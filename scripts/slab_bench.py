@@ -75,6 +75,7 @@ def main():
     ap.add_argument("--nx-inner", type=int, default=8000)
     ap.add_argument("--nz-inner", type=int, default=4000)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--sync-exchange", action="store_true", help="host-synchronised halo exchange (debug)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -94,7 +95,7 @@ def main():
                 ix_sources=[nxi // 2], iz_sources=[20], moment_angles=[90.0], which_source_to_fire_in_which_shot=[[0]],
                 nr=64, ix_receivers=[int(x) for x in np.linspace(100, nxi - 100, 64)], iz_receivers=[10] * 64,
                 snapshot_interval=50, npx=1, npz=1)
-    d = psvwave_b200.SlabDomain(ini, halo_steps=args.halo_steps)
+    d = psvwave_b200.SlabDomain(ini, halo_steps=args.halo_steps, async_exchange=not args.sync_exchange)
     for k, m in enumerate(d.slabs):  # homogeneous + one seeded anomaly, set slab by slab (no whole-grid host array)
         a, b = d._rows(k)
         x = np.arange(a, b)[:, None]
@@ -124,7 +125,7 @@ def main():
     if rank == 0:
         updates = 2.0 * d.nx * d.nz * d.nt
         print(json.dumps({"workload": "C5-large-grid-forward+adjoint", "grid": [d.nx, d.nz], "nt": d.nt, "n_gpus": world,
-                          "halo_rows": d.halo_rows, "exchanges_per_march": d.exchanges, "scaling": "strong",
+                          "halo_rows": d.halo_rows, "stream_ordered_exchange": bool(world > 1 and d._stream_ordered()), "exchanges_per_march": d.exchanges, "scaling": "strong",
                           "seconds": dt, "updates_per_s": updates / dt, "adjoint_device_ms_rank0": dev_ms,
                           "misfit": d.misfit,
                           "halo_bytes_per_exchange_per_side": 5 * d.halo_rows * int(d.info[0]["pitch"]) * 8}), flush=True)
