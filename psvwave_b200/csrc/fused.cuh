@@ -134,9 +134,31 @@ __device__ __forceinline__ void window_from_global(const double *ovx, const doub
   w.vz_0 = __ldg(reinterpret_cast<const double2 *>(ovz) + r);
 }
 
+// What the correlation of one row needs besides the march's own data: the forward snapshot
+// (5 fields) and the three Lame kernels it adds to.
+struct CorrData {
+  double2 fvx, fvz, fxx, fzz, fxz, kr, kl, km;
+};
+__device__ __forceinline__ void corr_from_global(const FusedCommon &c, const FusedModel &m, long long r, CorrData &q) {
+  const double *s = m.snap + c.snap_offset;
+  q.fvx = ld2s(s, r);
+  q.fvz = ld2s(s + c.snap_field_stride, r);
+  q.fxx = ld2s(s + 2 * c.snap_field_stride, r);
+  q.fzz = ld2s(s + 3 * c.snap_field_stride, r);
+  q.fxz = ld2s(s + 4 * c.snap_field_stride, r);
+  q.kr = *(reinterpret_cast<const double2 *>(m.k_rho) + r);
+  q.kl = *(reinterpret_cast<const double2 *>(m.k_lam) + r);
+  q.km = *(reinterpret_cast<const double2 *>(m.k_mu) + r);
+}
+
 struct GlobalRows {
   const double *ovx, *ovz, *oxx, *ozz, *oxz, *lm, *mu, *b;
   long long ld2n;
+  __device__ __forceinline__ void fetch_corr(const FusedCommon &c, const FusedModel &m, long long r, bool lane_ok,
+                                             CorrData &q) const {
+    if (lane_ok) corr_from_global(c, m, r, q);
+  }
+  __device__ __forceinline__ void release() const {}
   __device__ __forceinline__ void prologue(int, long long r, MarchWindow &w) const {
     window_from_global(ovx, ovz, r, ld2n, w);
   }
@@ -239,24 +261,22 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         st2s(s + 4 * c.snap_field_stride, r, txz);
       }
       if (MODE == MODE_ACCUMULATE) {
-        if (mine && j >= c.wx0 && j < c.wx1 && z0 + 1 >= c.wz0 && z0 < c.wz1) {
-          const double *s = m.snap + c.snap_offset;
-          const double2 fvx = ld2s(s, r), fvz = ld2s(s + c.snap_field_stride, r),
-                        fxx = ld2s(s + 2 * c.snap_field_stride, r),
-                        fzz = ld2s(s + 3 * c.snap_field_stride, r),
-                        fxz = ld2s(s + 4 * c.snap_field_stride, r);
-          double2 kr = *(reinterpret_cast<const double2 *>(m.k_rho) + r),
-                  kl = *(reinterpret_cast<const double2 *>(m.k_lam) + r),
-                  km = *(reinterpret_cast<const double2 *>(m.k_mu) + r);
-          if (z0 >= c.wz0 && z0 < c.wz1)
-            kernel_accumulate<M>(c.sidt, lm.x, mu.x, fvx.x, fvz.x, fxx.x, fzz.x, fxz.x, vx_0.x, vz_0.x,
-                                 txx.x, tzz.x, txz.x, kr.x, kl.x, km.x);
-          if (z0 + 1 >= c.wz0 && z0 + 1 < c.wz1)
-            kernel_accumulate<M>(c.sidt, lm.y, mu.y, fvx.y, fvz.y, fxx.y, fzz.y, fxz.y, vx_0.y, vz_0.y,
-                                 txx.y, tzz.y, txz.y, kr.y, kl.y, km.y);
-          st2s(m.k_rho, r, kr);
-          st2s(m.k_lam, r, kl);
-          st2s(m.k_mu, r, km);
+        if (j >= c.wx0 && j < c.wx1) {  // warp-uniform: the row source stages the extra arrays for exactly these rows
+          const bool lane_ok = mine && z0 + 1 >= c.wz0 && z0 < c.wz1;
+          CorrData q;
+          q.kr = q.kl = q.km = q.fvx = q.fvz = q.fxx = q.fzz = q.fxz = make_double2(0.0, 0.0);
+          rows.fetch_corr(c, m, r, lane_ok, q);
+          if (lane_ok) {
+            if (z0 >= c.wz0 && z0 < c.wz1)
+              kernel_accumulate<M>(c.sidt, lm.x, mu.x, q.fvx.x, q.fvz.x, q.fxx.x, q.fzz.x, q.fxz.x, vx_0.x, vz_0.x,
+                                   txx.x, tzz.x, txz.x, q.kr.x, q.kl.x, q.km.x);
+            if (z0 + 1 >= c.wz0 && z0 + 1 < c.wz1)
+              kernel_accumulate<M>(c.sidt, lm.y, mu.y, q.fvx.y, q.fvz.y, q.fxx.y, q.fzz.y, q.fxz.y, vx_0.y, vz_0.y,
+                                   txx.y, tzz.y, txz.y, q.kr.y, q.kl.y, q.km.y);
+            st2s(m.k_rho, r, q.kr);
+            st2s(m.k_lam, r, q.kl);
+            st2s(m.k_mu, r, q.km);
+          }
         }
       }
       // receiver sampling from the old velocities (src/fdModel.cpp:576-596)
@@ -279,6 +299,8 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         }
       }
     }
+
+    rows.release();  // the row's slot of a shared-memory ring can be refilled from here on
 
     // ---- stress update of row j (all lanes: halo lanes feed their neighbours; masked points
     //      keep their value through selects, not branches) ----
@@ -481,6 +503,11 @@ struct PipeGeom {
   static constexpr int kStage = kSeg * kPipeArrays;     // bytes of one ring slot
 };
 
+// Segments of one ring slot: the 8 arrays of the march, plus -- in correlation launches, for the rows
+// of the free window -- the 5 snapshot fields and the 3 Lame kernels (src/fdModel.cpp:817-861), so
+// that the correlation reads ride the same TMA pipeline instead of stalling the march on global loads.
+constexpr int kPipeArraysCorr = 16;
+
 // Row source of variant 3: the ring in shared memory.
 struct PipeRows {
   const unsigned char *ring;  // first slot
@@ -492,6 +519,7 @@ struct PipeRows {
   int lane;
   const double *ovx, *ovz;    // old velocities in global memory (window fill)
   long long ld2n;
+  bool has_corr;              // correlation rows carry segments 8..15
   __device__ __forceinline__ void prologue(int, long long r, MarchWindow &w) const {
     window_from_global(ovx, ovz, r, ld2n, w);
   }
@@ -506,6 +534,25 @@ struct PipeRows {
     d.lm = *reinterpret_cast<const double2 *>(s + 5 * seg);
     d.mu = *reinterpret_cast<const double2 *>(s + 6 * seg);
     d.b = *reinterpret_cast<const double2 *>(s + 7 * seg);
+  }
+  __device__ __forceinline__ void fetch_corr(const FusedCommon &c, const FusedModel &m, long long r, bool lane_ok,
+                                             CorrData &q) const {
+    if (has_corr) {
+      const unsigned char *s = ring + (size_t)slot * stage_bytes + lane_off;
+      q.fvx = *reinterpret_cast<const double2 *>(s + 8 * seg);
+      q.fvz = *reinterpret_cast<const double2 *>(s + 9 * seg);
+      q.fxx = *reinterpret_cast<const double2 *>(s + 10 * seg);
+      q.fzz = *reinterpret_cast<const double2 *>(s + 11 * seg);
+      q.fxz = *reinterpret_cast<const double2 *>(s + 12 * seg);
+      q.kr = *reinterpret_cast<const double2 *>(s + 13 * seg);
+      q.kl = *reinterpret_cast<const double2 *>(s + 14 * seg);
+      q.km = *reinterpret_cast<const double2 *>(s + 15 * seg);
+    } else if (lane_ok) {
+      corr_from_global(c, m, r, q);
+    }
+  }
+  // hand the slot back (everything this warp wants from it sits in registers)
+  __device__ __forceinline__ void release() {
     __syncwarp();
     if (lane == 0) mbar_arrive(empty0 + 8 * slot);
     if (++slot == stages) {
@@ -524,6 +571,7 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
   unsigned long long *bars = reinterpret_cast<unsigned long long *>(psv_smem);  // [stages] full, [stages] empty
   unsigned char *ring = psv_smem + 128 * ((2 * stages * 8 + 127) / 128);
   const unsigned full0 = smem_u32(bars), empty0 = full0 + 8 * stages;
+  constexpr int kSlotBytes = G::kSeg * (MODE == MODE_ACCUMULATE ? kPipeArraysCorr : kPipeArrays);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -550,16 +598,30 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
       int slot = 0;
       unsigned phase = 0;
       const unsigned ring_u32 = smem_u32(ring);
+      // correlation rows (the consumers use the same predicate: row of this strip inside the free window)
+      const int cx0 = max(xs, c.wx0), cx1 = min(xe, c.wx1);
+      const double *snap0 = MODE == MODE_ACCUMULATE ? m.snap + c.snap_offset : nullptr;
       for (int j = xs - 2; j < xe + 2; ++j) {
         mbar_wait(empty0 + 8 * slot, phase ^ 1);
         const unsigned bar = full0 + 8 * slot;
-        mbar_expect_tx(bar, G::kStage);
-        const unsigned dst = ring_u32 + slot * G::kStage;
+        const bool corr = MODE == MODE_ACCUMULATE && j >= cx0 && j < cx1;
+        mbar_expect_tx(bar, corr ? G::kSeg * kPipeArraysCorr : G::kStage);
+        const unsigned dst = ring_u32 + slot * kSlotBytes;
 #pragma unroll
         for (int a = 0; a < kPipeArrays; ++a)
           bulk_g2s(dst + a * G::kSeg,
                    reinterpret_cast<const double2 *>(src[a]) + ((long long)j + row_off[a]) * ld2n + kp_tile,
                    G::kSeg, bar);
+        if (corr) {
+          const long long off = (long long)j * ld2n + kp_tile;
+#pragma unroll
+          for (int f = 0; f < 5; ++f)
+            bulk_g2s(dst + (8 + f) * G::kSeg, reinterpret_cast<const double2 *>(snap0 + f * c.snap_field_stride) + off,
+                     G::kSeg, bar);
+          bulk_g2s(dst + 13 * G::kSeg, reinterpret_cast<const double2 *>(m.k_rho) + off, G::kSeg, bar);
+          bulk_g2s(dst + 14 * G::kSeg, reinterpret_cast<const double2 *>(m.k_lam) + off, G::kSeg, bar);
+          bulk_g2s(dst + 15 * G::kSeg, reinterpret_cast<const double2 *>(m.k_mu) + off, G::kSeg, bar);
+        }
         if (++slot == stages) {
           slot = 0;
           phase ^= 1;
@@ -570,8 +632,8 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
   }
 
   // ---- consumers ----
-  PipeRows rows{ring, full0, empty0, stages, G::kSeg, G::kStage, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane,
-                m.f[c.parity][0], m.f[c.parity][1], ld2n};
+  PipeRows rows{ring, full0, empty0, stages, G::kSeg, kSlotBytes, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane,
+                m.f[c.parity][0], m.f[c.parity][1], ld2n, MODE == MODE_ACCUMULATE};
   const int kp = kp_tile + warp * kFusedOwnedPairs + lane;
   const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
   GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],

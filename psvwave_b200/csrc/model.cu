@@ -131,7 +131,7 @@ void Model::allocate() {
   // the ten state arrays (2 buffers x vx vz txx tzz txz) sit in ONE allocation at a constant stride
   field_stride_ = grid_elems_ + 2 * guard_;
   fields_.allocate(10 * field_stride_ * sizeof(double));
-  lame_kernels_.allocate(3 * grid_elems_ * sizeof(double));
+  lame_kernels_.allocate((3 * grid_elems_ + 2 * kBulkPad) * sizeof(double));
   taper_table_.allocate((c.np_boundary + 1) * sizeof(double));
   stf_.allocate((size_t)c.n_sources * c.nt * sizeof(double));
   const size_t rec = (size_t)c.n_shots * c.nr * c.nt * sizeof(double);
@@ -418,7 +418,7 @@ void Model::zero_dynamic_fields() {
 
 void Model::ensure_snapshots(int i_shot) {
   DeviceBuffer &s = snapshots_[i_shot];
-  const size_t bytes = 5 * (size_t)n_snap_alloc_ * grid_elems_ * sizeof(double);
+  const size_t bytes = (5 * (size_t)n_snap_alloc_ * grid_elems_ + 2 * kBulkPad) * sizeof(double);
   if (s.empty() && !snapshot_pool_.empty()) {
     // a pooled buffer may hold another shot's snapshots: every snapshot the adjoint reads is
     // rewritten by the stored forward run, and get_array reports only shots stored since
@@ -441,7 +441,7 @@ void Model::ensure_snapshots(int i_shot) {
 }
 
 double *Model::snapshot_ptr(int i_shot, int field, int snap) const {
-  return snapshots_[i_shot].as<double>() + ((size_t)field * n_snap_alloc_ + snap) * grid_elems_;
+  return snapshots_[i_shot].as<double>() + kBulkPad + ((size_t)field * n_snap_alloc_ + snap) * grid_elems_;
 }
 
 void Model::release_snapshots(int i_shot) {
@@ -458,7 +458,7 @@ void Model::release_snapshots(int i_shot) {
 }
 
 void Model::kernel_buffer(void **ptr, size_t *count) const {
-  *ptr = lame_kernels_.as<double>();
+  *ptr = lame();
   *count = 3 * grid_elems_;
 }
 
@@ -517,9 +517,9 @@ void Model::launch_stress(double sdt, int mode, int i_shot, int snap) {
     a.s_txz = snapshot_ptr(i_shot, 4, snap);
   }
   if (mode == MODE_ACCUMULATE) {
-    a.k_lam = lame_kernels_.as<double>();
-    a.k_mu = lame_kernels_.as<double>() + grid_elems_;
-    a.k_rho = lame_kernels_.as<double>() + 2 * grid_elems_;
+    a.k_lam = lame();
+    a.k_mu = lame() + grid_elems_;
+    a.k_rho = lame() + 2 * grid_elems_;
     a.wx0 = c.np_boundary + c.nx_inner_boundary;
     a.wx1 = c.np_boundary + c.nx_inner - c.nx_inner_boundary;
     a.wz0 = c.np_boundary + c.nz_inner_boundary;
@@ -559,10 +559,10 @@ void Model::fill_fused_model(int i_shot, void *out) const {
   fm.lm = lm_.data();
   fm.mu = mu_.data();
   fm.b = b_.data();
-  fm.snap = snapshots_[i_shot].empty() ? nullptr : snapshots_[i_shot].as<double>();
-  fm.k_lam = lame_kernels_.as<double>();
-  fm.k_mu = lame_kernels_.as<double>() + grid_elems_;
-  fm.k_rho = lame_kernels_.as<double>() + 2 * grid_elems_;
+  fm.snap = snapshots_[i_shot].empty() ? nullptr : snapshots_[i_shot].as<double>() + kBulkPad;
+  fm.k_lam = lame();
+  fm.k_mu = lame() + grid_elems_;
+  fm.k_rho = lame() + 2 * grid_elems_;
   const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
   fm.ux = rtf_ux_.as<>() + shot_rows;
   fm.uz = rtf_uz_.as<>() + shot_rows;
@@ -633,8 +633,15 @@ void launch_pipe_m(int mode, const FusedCommon &fc, const FusedModel *models, di
   else launch_pipe_k<M, MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
 }
 template <int NW>
-size_t pipe_smem_bytes(int stages) {
-  return 128 * ((2 * (size_t)stages * 8 + 127) / 128) + (size_t)stages * PipeGeom<NW>::kStage;
+size_t pipe_smem_bytes(int stages, int arrays = kPipeArrays) {
+  return 128 * ((2 * (size_t)stages * 8 + 127) / 128) + (size_t)stages * PipeGeom<NW>::kSeg * arrays;
+}
+constexpr size_t kMaxPipeSmem = 232448;  // 227 KB per CTA on sm_100
+// correlation launches stage 16 segments per row: as many ring slots as fit, at most `stages`
+template <int NW>
+int pipe_corr_stages(int stages) {
+  while (stages > 2 && pipe_smem_bytes<NW>(stages, kPipeArraysCorr) > kMaxPipeSmem) --stages;
+  return stages;
 }
 }  // namespace
 
@@ -895,15 +902,22 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     fc.strip = strip;
     dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
     const int nw = pipe_warps();
+    int stages = pipe_stages_;
+    if (mode == MODE_ACCUMULATE) {
+      stages = nw == 8 ? pipe_corr_stages<8>(stages) : nw == 4 ? pipe_corr_stages<4>(stages) : pipe_corr_stages<3>(stages);
+      smem = nw == 8   ? pipe_smem_bytes<8>(stages, kPipeArraysCorr)
+             : nw == 4 ? pipe_smem_bytes<4>(stages, kPipeArraysCorr)
+                       : pipe_smem_bytes<3>(stages, kPipeArraysCorr);
+    }
     if (nw == 8) {
-      if (exact_) launch_pipe_m<ExactMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
-      else launch_pipe_m<FastMath, 8>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      if (exact_) launch_pipe_m<ExactMath, 8>(mode, fc, models, grid, stages, smem, stream_);
+      else launch_pipe_m<FastMath, 8>(mode, fc, models, grid, stages, smem, stream_);
     } else if (nw == 4) {
-      if (exact_) launch_pipe_m<ExactMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
-      else launch_pipe_m<FastMath, 4>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      if (exact_) launch_pipe_m<ExactMath, 4>(mode, fc, models, grid, stages, smem, stream_);
+      else launch_pipe_m<FastMath, 4>(mode, fc, models, grid, stages, smem, stream_);
     } else {
-      if (exact_) launch_pipe_m<ExactMath, 3>(mode, fc, models, grid, pipe_stages_, smem, stream_);
-      else launch_pipe_m<FastMath, 3>(mode, fc, models, grid, pipe_stages_, smem, stream_);
+      if (exact_) launch_pipe_m<ExactMath, 3>(mode, fc, models, grid, stages, smem, stream_);
+      else launch_pipe_m<FastMath, 3>(mode, fc, models, grid, stages, smem, stream_);
     }
   } else {
     const int wpb = fused_block_ / 32;
@@ -1456,7 +1470,7 @@ void Model::reset_kernels() {
 
 void Model::map_kernels_to_velocity() {
   bind();
-  double *k = lame_kernels_.as<double>();
+  double *k = lame();
   map_kernels_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(
       vp_.data(), vs_.data(), b_.data(), k, k + grid_elems_, k + 2 * grid_elems_, vp_kernel_.data(),
       vs_kernel_.data(), density_v_kernel_.data(), grid_elems_);
@@ -1542,7 +1556,7 @@ void Model::get_array(psv_array which, double *out, size_t count) {
   PSV_CUDA(cudaStreamSynchronize(stream_));
   const Config &c = cfg_;
   const size_t grid = (size_t)c.nx * c.nz;
-  double *k = lame_kernels_.as<double>();
+  double *k = lame();
   switch (which) {
     case PSV_VX: return grid_to_host(F(0), out);
     case PSV_VZ: return grid_to_host(F(1), out);
@@ -1619,7 +1633,7 @@ void Model::set_array(psv_array which, const double *in, size_t count) {
   bind();
   if (count != array_size(which)) throw invalid_argument("Array size mismatch.");
   PSV_CUDA(cudaStreamSynchronize(stream_));
-  double *k = lame_kernels_.as<double>();
+  double *k = lame();
   switch (which) {
     case PSV_VP: return grid_from_host(vp_.data(), in);
     case PSV_VS: return grid_from_host(vs_.data(), in);

@@ -177,6 +177,11 @@ class Model {
   void win_geometry(int batch, int *tiles, int *strip);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
   void pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem);
+  // Slack (in doubles) before and after the snapshot and Lame-kernel allocations: the bulk copies of
+  // the correlation launches read whole row segments, which start 2 pairs before a row and may run
+  // past its end by a tile's tail.
+  static constexpr size_t kBulkPad = 1024;
+  double *lame() const { return lame_kernels_.as<double>() + kBulkPad; }
   double *field_ptr(int p, int k) const { return fields_.as<double>() + (size_t)(5 * p + k) * field_stride_ + guard_; }
   double *F(int k) const { return field_ptr(cur_, k); }  // current state: vx vz txx tzz txz
   void write_wavefield_files(int it);

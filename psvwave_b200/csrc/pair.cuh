@@ -167,9 +167,15 @@ struct PairRows {
     d.lm = lift(j, 5);
     d.mu = lift(j, 6);
     d.b = lift(j, 7);
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty0 + 8 * slot_of(j));
+    cur = j;
   }
+  // stage B runs plain steps only (the host never pairs a step whose second half correlates)
+  __device__ __forceinline__ void fetch_corr(const FusedCommon &, const FusedModel &, long long, bool, CorrData &) const {}
+  __device__ __forceinline__ void release() {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty0 + 8 * slot_of(cur));
+  }
+  int cur;
 };
 
 // Row source of stage A: ring T as in variant 3, but without a producer warp -- 2*NW warps fill
@@ -222,9 +228,18 @@ struct SelfFedRows {
     ring.prologue(j, r, w);
   }
   __device__ __forceinline__ void fetch(int j, long long r, RowData &d) {
-    ring.fetch(j, r, d);        // consumes row j and releases its slot (this warp's share)
-    feed(j + ring.stages - 1);  // refill; blocks until the slowest stage-A warp has left row j - 1
+    ring.fetch(j, r, d);  // consumes row j
+    cur = j;
   }
+  __device__ __forceinline__ void fetch_corr(const FusedCommon &c, const FusedModel &fm, long long r, bool lane_ok,
+                                             CorrData &q) const {
+    ring.fetch_corr(c, fm, r, lane_ok, q);  // ring T carries no correlation segments: straight from global memory
+  }
+  __device__ __forceinline__ void release() {
+    ring.release();               // this warp's share of the slot
+    feed(cur + ring.stages - 1);  // refill; blocks until the slowest stage-A warp has left row cur - 1
+  }
+  int cur;
 };
 
 template <class M, int MODE, int NW>
@@ -266,9 +281,9 @@ __global__ void __launch_bounds__(2 * NW * 32) fused_pair_kernel(const FusedComm
   if (warp < NW) {
     // ---- stage A: state t -> t+1, ring T -> ring X ----
     PipeRows ring{ring_t, full_t, empty_t, stages, G::kSegT, G::kStageT, (warp * kFusedOwnedPairs + lane) * 16,
-                  0,      0u,     lane,    m.f[c.parity][0], m.f[c.parity][1], ld2n};
+                  0,      0u,     lane,    m.f[c.parity][0], m.f[c.parity][1], ld2n, false};
     SelfFedRows<G::kSegT> rows{ring, &m, m.f[c.parity][0], c.field_stride, ld2n, kp_t, xsA - 2, xeA + 1,
-                               warp == 0 && lane == 0, 0, 0u};
+                               warp == 0 && lane == 0, 0, 0u, 0};
     const int kp = kp_t + warp * kFusedOwnedPairs + lane;
     const bool own = lane >= 2 && lane < 30;
     const bool mine = own && kp >= tb0 && kp < tb0 + c.tile_pairs && kp < (int)ld2n;
@@ -284,7 +299,7 @@ __global__ void __launch_bounds__(2 * NW * 32) fused_pair_kernel(const FusedComm
     const int idx = wb * kFusedOwnedPairs + lane;  // position inside stage A's owned range
     const bool inside = idx < G::kOwnedA;
     PairRows rows{ring_x, full_x, empty_x, G::kSegX, G::kSlotX, (inside ? idx : 0) * 16,
-                  xsA - 2, xeA + 1, xsA,   xeA,      lane,     xsA - 2, 0, 0u};
+                  xsA - 2, xeA + 1, xsA,   xeA,      lane,     xsA - 2, 0, 0u, 0};
     const int kp = ta0 + idx;
     const bool own = lane >= 2 && lane < 30 && kp >= tb0 && kp < tb0 + c.tile_pairs && kp < (int)ld2n;
     GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
