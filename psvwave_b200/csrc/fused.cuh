@@ -69,6 +69,7 @@ struct FusedCommon {
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
   int tile_pairs;   // variant 5: z-pairs per CTA tile
+  int l2_mode;      // variant 3: bit 0 = medium rows evict_last in L2, bit 1 = state rows evict_first
   int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
   size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
   // snapshots / kernel accumulation
@@ -495,6 +496,26 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
                : "memory");
 }
 
+// The same copy with an L2 eviction-priority hint (createpolicy): the medium arrays are re-read by
+// every time step and fit (partly) in the 126 MB L2, the state arrays stream through.
+__device__ __forceinline__ void bulk_g2s_hint(unsigned dst, const void *src, unsigned bytes, unsigned bar,
+                                              unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
 template <int NW>
 struct PipeGeom {
   static constexpr int kOwned = NW * kFusedOwnedPairs;  // pairs owned by the CTA
@@ -600,6 +621,7 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
       const unsigned ring_u32 = smem_u32(ring);
       // correlation rows (the consumers use the same predicate: row of this strip inside the free window)
       const int cx0 = max(xs, c.wx0), cx1 = min(xe, c.wx1);
+      const unsigned long long keep = l2_policy_evict_last(), stream = l2_policy_evict_first();
       const double *snap0 = MODE == MODE_ACCUMULATE ? m.snap + c.snap_offset : nullptr;
       for (int j = xs - 2; j < xe + 2; ++j) {
         mbar_wait(empty0 + 8 * slot, phase ^ 1);
@@ -608,10 +630,13 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
         mbar_expect_tx(bar, corr ? G::kSeg * kPipeArraysCorr : G::kStage);
         const unsigned dst = ring_u32 + slot * kSlotBytes;
 #pragma unroll
-        for (int a = 0; a < kPipeArrays; ++a)
-          bulk_g2s(dst + a * G::kSeg,
-                   reinterpret_cast<const double2 *>(src[a]) + ((long long)j + row_off[a]) * ld2n + kp_tile,
-                   G::kSeg, bar);
+        for (int a = 0; a < kPipeArrays; ++a) {
+          const double2 *from = reinterpret_cast<const double2 *>(src[a]) + ((long long)j + row_off[a]) * ld2n + kp_tile;
+          const bool medium = a >= 5;
+          if (medium && (c.l2_mode & 1)) bulk_g2s_hint(dst + a * G::kSeg, from, G::kSeg, bar, keep);
+          else if (!medium && (c.l2_mode & 2)) bulk_g2s_hint(dst + a * G::kSeg, from, G::kSeg, bar, stream);
+          else bulk_g2s(dst + a * G::kSeg, from, G::kSeg, bar);
+        }
         if (corr) {
           const long long off = (long long)j * ld2n + kp_tile;
 #pragma unroll

@@ -337,6 +337,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   pipe_stages_ = o.pipe_stages_;
   win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
+  l2_mode_ = o.l2_mode_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
     if (src.empty()) return;
@@ -769,7 +770,9 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
     const int n_strips = std::max(1, waves * pipe_resident_ / blocks_x);
     const int st = (nx + n_strips - 1) / n_strips;
     if (st <= 128 || n_strips >= nx) {
-      *strip = std::max(st, 8);
+      // small grids are bound by the serial latency of a CTA's march (~1 us per row), so short strips
+      // win although each recomputes 4 halo rows: 250x150, one model: 15.3 -> 10.2 us per step with 2 rows
+      *strip = std::max(st, 2);
       return;
     }
   }
@@ -856,6 +859,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1 + (int)batch_followers_.size()));
   fc.tile_pairs = 0;
   fc.it_step = 0;
+  fc.l2_mode = l2_mode_;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
   // free window in local rows; a slab correlates only on the rows it owns
@@ -1866,6 +1870,9 @@ void Model::set_option(const std::string &name, long long v) {
     if (v < 0 || v >= kWinConfigCount) throw invalid_argument("win_config out of range");
     win_config_ = (int)v;
     win_resident_ = 0;
+  } else if (name == "l2_mode") {
+    if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
+    l2_mode_ = (int)v;
   } else if (name == "pipe_stages") {
     if (v < 2 || v > 16) throw invalid_argument("pipe_stages must be in 2..16");
     pipe_stages_ = (int)v;
@@ -1908,6 +1915,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "pipe_stages") return pipe_stages_;
   if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps();
+  if (name == "l2_mode") return l2_mode_;
   if (name == "pair_warps") return pair_warps_;
   if (name == "pair_stages") return pair_stages_;
   if (name == "pair_strip") return pair_strip_;

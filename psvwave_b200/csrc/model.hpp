@@ -241,6 +241,7 @@ class Model {
   int fused_resident_blocks_ = 0;
   int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
   int win_config_ = 0, win_resident_ = 0;
+  int l2_mode_ = 0;  // L2 eviction hints of the variant-3 bulk copies (fused.cuh)
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;
   double stat_pair_ms_ = 0;
