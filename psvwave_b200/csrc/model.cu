@@ -11,6 +11,7 @@
 #include <sstream>
 
 #include "fused.cuh"
+#include "fused32.cuh"
 #include "kernels.cuh"
 #include "pointwise.cuh"
 #include "pair.cuh"
@@ -338,6 +339,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
   l2_mode_ = o.l2_mode_;
+  fp32_ = o.fp32_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
     if (src.empty()) return;
@@ -350,6 +352,8 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   for (size_t i = 0; i < sizeof(gs) / sizeof(gs[0]); ++i) dcopy(gs[i]->buf, gd[i]->buf);
   cur_ = o.cur_;
   dcopy(o.fields_, fields_);
+  dcopy(o.fields32_, fields32_);
+  dcopy(o.medium32_, medium32_);
   dcopy(o.lame_kernels_, lame_kernels_);
   dcopy(o.taper_table_, taper_table_);
   dcopy(o.stf_, stf_);
@@ -413,13 +417,14 @@ void Model::check_shot(int i_shot) const {
 }
 
 void Model::zero_dynamic_fields() {
+  if (fp32_) PSV_CUDA(cudaMemsetAsync(fields32_.as<char>(), 0, fields32_.bytes(), stream_));
   PSV_CUDA(cudaMemsetAsync(fields_.as<char>(), 0, fields_.bytes(), stream_));
   cur_ = 0;
 }
 
 void Model::ensure_snapshots(int i_shot) {
   DeviceBuffer &s = snapshots_[i_shot];
-  const size_t bytes = (5 * (size_t)n_snap_alloc_ * grid_elems_ + 2 * kBulkPad) * sizeof(double);
+  const size_t bytes = (5 * (size_t)n_snap_alloc_ * grid_elems_ + 2 * kBulkPad) * (fp32_ ? sizeof(float) : sizeof(double));
   if (s.empty() && !snapshot_pool_.empty()) {
     // a pooled buffer may hold another shot's snapshots: every snapshot the adjoint reads is
     // rewritten by the stored forward run, and get_array reports only shots stored since
@@ -582,6 +587,60 @@ void Model::fused_begin(int i_shot, int point_mode) {
   if (fused_model_.bytes() < bytes) fused_model_.allocate(bytes);
   // stream-ordered upload from a local object: wait for it before the object dies
   copy_sync(fused_model_.as<FusedModel>(), fm.data(), bytes, cudaMemcpyHostToDevice);
+  if (fp32_) {
+    std::vector<FusedModel32> f32(1 + batch_followers_.size());
+    fill_fused_model32(i_shot, &f32[0]);
+    for (size_t i = 0; i < batch_followers_.size(); ++i) batch_followers_[i]->fill_fused_model32(i_shot, &f32[i + 1]);
+    const size_t b32 = f32.size() * sizeof(FusedModel32);
+    if (fused_model32_.bytes() < b32) fused_model32_.allocate(b32);
+    copy_sync(fused_model32_.as<FusedModel32>(), f32.data(), b32, cudaMemcpyHostToDevice);
+  }
+}
+
+// ---- optional FP32 wavefield mode (fused32.cuh) -----------------------------------------------
+void Model::ensure_fp32() {
+  if (fields32_.empty()) {
+    fields32_.allocate(10 * field_stride_ * sizeof(float));
+    medium32_.allocate(3 * field_stride_ * sizeof(float));
+  }
+  refresh_medium32();
+}
+
+void Model::refresh_medium32() {  // float images of lm, mu, b (pad columns included, guards stay zero)
+  const double *src[3] = {lm_.data(), mu_.data(), b_.data()};
+  for (int k = 0; k < 3; ++k)
+    to_float_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(src[k], medium32_ptr(k), grid_elems_);
+  PSV_CUDA(cudaGetLastError());
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::fill_fused_model32(int i_shot, void *out) const {
+  const Config &c = cfg_;
+  FusedModel32 fm{};
+  for (int p = 0; p < 2; ++p)
+    for (int k = 0; k < 5; ++k) fm.f[p][k] = field32_ptr(p, k);
+  fm.lm = medium32_ptr(0);
+  fm.mu = medium32_ptr(1);
+  fm.b = medium32_ptr(2);
+  fm.snap = snapshots_[i_shot].empty() ? nullptr : snapshots_[i_shot].as<float>() + kBulkPad;
+  fm.k_lam = lame();
+  fm.k_mu = lame() + grid_elems_;
+  fm.k_rho = lame() + 2 * grid_elems_;
+  const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
+  fm.ux = rtf_ux_.as<>() + shot_rows;
+  fm.uz = rtf_uz_.as<>() + shot_rows;
+  fm.ax = a_stf_ux_.as<>() + shot_rows;
+  fm.az = a_stf_uz_.as<>() + shot_rows;
+  *static_cast<FusedModel32 *>(out) = fm;
+}
+
+// Current state array k as doubles: the array itself, or (FP32 mode) a converted image.
+const double *Model::field_as_double(int k) {
+  if (!fp32_) return F(k);
+  if (conv_.buf.empty()) conv_ = make_grid();
+  to_double_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(field32_ptr(cur_, k), conv_.data(), grid_elems_);
+  PSV_CUDA(cudaGetLastError());
+  return conv_.data();
 }
 
 namespace {
@@ -881,7 +940,16 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.stf = stf_.as<>();
   const FusedModel *models = fused_model_.as<FusedModel>();
   const int batch = 1 + (int)batch_followers_.size();
-  if (variant_ == 5 && pair_step != 0) {
+  if (fp32_) {
+    if (slab_) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
+    fc.strip = fused_strip_ > 0 ? fused_strip_ : fused_auto_strip(fc.n_zwarps, batch);
+    const int wpb = 4;
+    dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
+    const FusedModel32 *m32 = fused_model32_.as<FusedModel32>();
+    if (mode == MODE_SNAPSHOT) fused32_step_kernel<MODE_SNAPSHOT><<<grid, 128, 0, stream_>>>(fc, m32);
+    else if (mode == MODE_ACCUMULATE) fused32_step_kernel<MODE_ACCUMULATE><<<grid, 128, 0, stream_>>>(fc, m32);
+    else fused32_step_kernel<MODE_PLAIN><<<grid, 128, 0, stream_>>>(fc, m32);
+  } else if (variant_ == 5 && pair_step != 0) {
     int tiles = 0, tile_pairs = 0, strip = 0;
     size_t smem = 0;
     pair_geometry(batch, &tiles, &tile_pairs, &strip, &smem);
@@ -985,6 +1053,8 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
                       "(psvwave_b200.SlabDomain does).");
   bind();
   const Config &c = cfg_;
+  if (fp32_ && (variant_ < 2 || output_wavefields))
+    throw invalid_argument("The FP32 wavefield mode needs a fused variant (>= 2) and no wavefield dumps.");
   if (store_fields) ensure_snapshots(i_shot);
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
@@ -1005,7 +1075,7 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
     if (variant_ >= 2) {
       const bool snap = store_fields && it % c.snapshot_interval == 0;
       // variant 5 advances two steps per launch unless the second one has a snapshot to store
-      const bool pair = variant_ == 5 && !output_wavefields && it + 1 < c.nt &&
+      const bool pair = variant_ == 5 && !fp32_ && !output_wavefields && it + 1 < c.nt &&
                         !(store_fields && (it + 1) % c.snapshot_interval == 0);
       const bool sample = prof.sample(snap || (variant_ == 5 && !pair));
       if (sample) prof.mark(0);
@@ -1072,6 +1142,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   if (snapshots_[i_shot].empty())
     throw state_error("adjoint_simulate needs the forward wavefield of this shot: call "
                       "forward_simulate(i_shot, store_fields=True) first.");
+  if (fp32_ && variant_ < 2) throw invalid_argument("The FP32 wavefield mode needs a fused variant (>= 2).");
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
@@ -1087,7 +1158,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
     // variant 5 retreats two steps per launch unless the second one correlates with a snapshot
-    const bool pair = variant_ == 5 && it - 1 >= 0 && (it - 1) % c.snapshot_interval != 0;
+    const bool pair = variant_ == 5 && !fp32_ && it - 1 >= 0 && (it - 1) % c.snapshot_interval != 0;
     const bool sample = prof.sample(corr || (variant_ == 5 && !pair));
     if (variant_ >= 2) {
       if (sample) prof.mark(0);
@@ -1271,7 +1342,7 @@ void Model::check_batch(Model *const *models, int n, int i_shot) {
     for (int k = 0; k < i; ++k)
       if (models[k] == models[i]) throw invalid_argument("The same model appears twice in the batch.");
     const Config &p = a.cfg_, &q = b.cfg_;
-    const bool same = b.device_ == a.device_ && p.nx == q.nx && p.nz == q.nz && p.nt == q.nt && p.dx == q.dx &&
+    const bool same = b.device_ == a.device_ && b.fp32_ == a.fp32_ && p.nx == q.nx && p.nz == q.nz && p.nt == q.nt && p.dx == q.dx &&
                       p.dz == q.dz && p.dt == q.dt && p.np_boundary == q.np_boundary && p.np_factor == q.np_factor &&
                       p.nx_inner_boundary == q.nx_inner_boundary && p.nz_inner_boundary == q.nz_inner_boundary &&
                       p.snapshot_interval == q.snapshot_interval && p.peak_frequency == q.peak_frequency &&
@@ -1425,6 +1496,7 @@ void Model::update_from_velocity() {
       vp_.data(), vs_.data(), rho_.data(), lm_.data(), mu_.data(), b_.data(), grid_elems_);
   PSV_CUDA(cudaGetLastError());
   PSV_CUDA(cudaStreamSynchronize(stream_));
+  if (fp32_) refresh_medium32();
 }
 
 double Model::misfit_of_range(size_t first, size_t n) {
@@ -1562,11 +1634,11 @@ void Model::get_array(psv_array which, double *out, size_t count) {
   const size_t grid = (size_t)c.nx * c.nz;
   double *k = lame();
   switch (which) {
-    case PSV_VX: return grid_to_host(F(0), out);
-    case PSV_VZ: return grid_to_host(F(1), out);
-    case PSV_TXX: return grid_to_host(F(2), out);
-    case PSV_TZZ: return grid_to_host(F(3), out);
-    case PSV_TXZ: return grid_to_host(F(4), out);
+    case PSV_VX: return grid_to_host(field_as_double(0), out);
+    case PSV_VZ: return grid_to_host(field_as_double(1), out);
+    case PSV_TXX: return grid_to_host(field_as_double(2), out);
+    case PSV_TZZ: return grid_to_host(field_as_double(3), out);
+    case PSV_TXZ: return grid_to_host(field_as_double(4), out);
     case PSV_LM: return grid_to_host(lm_.data(), out);
     case PSV_MU: return grid_to_host(mu_.data(), out);
     case PSV_B_VX:
@@ -1620,6 +1692,13 @@ void Model::get_array(psv_array which, double *out, size_t count) {
         double *dst = out + (size_t)s * per_shot;
         if (snapshots_[s].empty() || per_shot == 0) {
           std::memset(dst, 0, per_shot * sizeof(double));
+        } else if (fp32_) {  // single-precision snapshots: one converted grid at a time
+          if (conv_.buf.empty()) conv_ = make_grid();
+          for (int k = 0; k < c.snapshots; ++k) {
+            const float *src = snapshots_[s].as<float>() + kBulkPad + ((size_t)field * n_snap_alloc_ + k) * grid_elems_;
+            to_double_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(src, conv_.data(), grid_elems_);
+            grid_to_host(conv_.data(), dst + (size_t)k * grid);
+          }
         } else {
           PSV_CUDA(cudaMemcpy2DAsync(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
                                      c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost,
@@ -1870,6 +1949,17 @@ void Model::set_option(const std::string &name, long long v) {
     if (v < 0 || v >= kWinConfigCount) throw invalid_argument("win_config out of range");
     win_config_ = (int)v;
     win_resident_ = 0;
+  } else if (name == "fp32") {
+    bind();
+    if (slab_ && v) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
+    if ((v != 0) != fp32_) {
+      PSV_CUDA(cudaStreamSynchronize(stream_));
+      for (DeviceBuffer &sn : snapshots_) sn.release();  // the element size of the snapshots changes
+      snapshot_pool_.clear();
+      fp32_ = v != 0;
+      if (fp32_) ensure_fp32();
+      zero_dynamic_fields();
+    }
   } else if (name == "l2_mode") {
     if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
     l2_mode_ = (int)v;
@@ -1916,6 +2006,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
+  if (name == "fp32") return fp32_ ? 1 : 0;
   if (name == "pair_warps") return pair_warps_;
   if (name == "pair_stages") return pair_stages_;
   if (name == "pair_strip") return pair_strip_;

@@ -169,6 +169,12 @@ class Model {
   // variant 2: one fused launch per time step (fused.cuh)
   void fused_begin(int i_shot, int point_mode);
   void fill_fused_model(int i_shot, void *out) const;
+  void fill_fused_model32(int i_shot, void *out) const;
+  void ensure_fp32();
+  void refresh_medium32();
+  const double *field_as_double(int k);
+  float *field32_ptr(int p, int k) const { return fields32_.as<float>() + (size_t)(5 * p + k) * field_stride_ + guard_; }
+  float *medium32_ptr(int k) const { return medium32_.as<float>() + (size_t)k * field_stride_ + guard_; }
   static void check_batch(Model *const *models, int n, int i_shot);
   void adopt_batch_state(const Model &leader);
   int fused_auto_strip(int n_zwarps, int batch);
@@ -222,6 +228,10 @@ class Model {
   DeviceBuffer rec_index_, rec_next_, rec_heads_;
   int n_rec_heads_ = 0;
   DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_;  // receivers bucketed by grid row (fused.cuh)
+  // optional FP32 wavefield mode (fused32.cuh): float images of the state and of lm mu b
+  bool fp32_ = false;
+  DeviceBuffer fields32_, medium32_, fused_model32_;
+  GridArray conv_;  // double image of one float grid array (getters)
   DeviceBuffer fused_model_;                             // FusedModel per batch member (device copy of the pointers)
   std::vector<Model *> batch_followers_;                 // non-empty only inside forward_batch / adjoint_batch
   std::vector<ShotPlan> plans_;
