@@ -358,10 +358,13 @@ def run_ours(args) -> None:
         pts = float(nx) * nz
         bytes_per_launch = {"stress": 12 * 8 * pts, "velocity": 10 * 8 * pts, "fused": 16 * 8 * pts}
         fused = m._get_option("variant") >= 2
+        fp32 = bool(m._get_option("fp32"))  # optional mode, never the default: words are 4 bytes there
+        if fp32:
+            bytes_per_launch = {k: v / 2 for k, v in bytes_per_launch.items()}
         if fused:
             ms = float(P[:, [0, 2]].mean())
             kern, nbytes = "fused stress+velocity sweep", bytes_per_launch["fused"]
-            if m._get_option("variant") == 5:
+            if m._get_option("variant") == 5 and not fp32:
                 # the sampled launches of variant 5 are its two-step launches: 2 grid-point updates
                 # per point, each credited with the single-pass 128 B
                 kern, nbytes = "fused two-step sweep", 2 * bytes_per_launch["fused"]
@@ -374,7 +377,7 @@ def run_ours(args) -> None:
         achieved = nbytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
+        if os.path.exists(tpath) and not fp32:  # the capture is of the default FP64 step kernel
             traffic = json.load(open(tpath)).get(kern)
         roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
@@ -388,7 +391,8 @@ def run_ours(args) -> None:
         line = {
             "metric": "grid-point updates/s (fwd+adj)", "value": value, "unit": "updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 wavefield, f64 seismograms/kernels (optional mode)" if fp32 else "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "grid": [nx, nz], "nt": nt, "snapshot_interval": m.snapshot_interval,
                        "shots_per_gpu_per_step": 1, "sources_per_shot": 2, "receivers": m.nr,
                        "step": "forward(store)+misfit+adjoint(+kernel accumulation)" + ("+allreduce" if world > 1 else ""),

@@ -26,7 +26,7 @@ HOST_CXX = "/usr/bin/g++"  # the image's $CXX wrapper (/opt/gcc) lacks a few spe
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 LIB_SOURCES = ["capi.cu", "model.cu", "config.cpp"]
-LIB_DEPS = LIB_SOURCES + ["model.hpp", "config.hpp", "kernels.cuh", "fused.cuh", "pair.cuh", "window.cuh", "pointwise.cuh", "stencil_math.cuh"]
+LIB_DEPS = LIB_SOURCES + ["model.hpp", "config.hpp", "kernels.cuh", "fused.cuh", "fused32.cuh", "pair.cuh", "window.cuh", "pointwise.cuh", "stencil_math.cuh"]
 
 
 def _stale(target: str, deps: list[str]) -> bool:

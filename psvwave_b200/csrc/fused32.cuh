@@ -99,12 +99,27 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
   float2 xz_m3 = zero2, xz_m2 = zero2, xz_m1 = zero2;
   float2 zz_m2 = zero2, zz_m1 = zero2;
 
+  // software pipeline: the 8 loads of row j+1 are issued before row j is computed, so a warp always
+  // has one row of memory latency in flight (the FP64 default gets the same from its TMA ring)
+  float2 n_vx = ld2f(ovx, r + 2 * ld2n), n_vz = ld2f(ovz, r + ld2n), n_xx = ld2f(oxx, r), n_zz = ld2f(ozz, r),
+         n_xz = ld2f(oxz, r), n_lm = ld2f(m.lm, r), n_mu = ld2f(m.mu, r), n_b = ld2f(m.b, r - 2 * ld2n);
 #pragma unroll 1
   for (; j < xe + 2; ++j, r += ld2n) {
-    const float2 vx_p2 = ld2f(ovx, r + 2 * ld2n), vz_p1 = ld2f(ovz, r + ld2n);
-    float2 txx = ld2f(oxx, r), tzz = ld2f(ozz, r), txz = ld2f(oxz, r);
-    const float2 lm = ld2f(m.lm, r), mu = ld2f(m.mu, r);
-    const float2 b = ld2f(m.b, r - 2 * ld2n);
+    const float2 vx_p2 = n_vx, vz_p1 = n_vz;
+    float2 txx = n_xx, tzz = n_zz, txz = n_xz;
+    const float2 lm = n_lm, mu = n_mu;
+    const float2 b = n_b;
+    {  // rows past the strip end fall into the guard band / the next strip's rows: harmless reads
+      const long long rn = r + ld2n;
+      n_vx = ld2f(ovx, rn + 2 * ld2n);
+      n_vz = ld2f(ovz, rn + ld2n);
+      n_xx = ld2f(oxx, rn);
+      n_zz = ld2f(ozz, rn);
+      n_xz = ld2f(oxz, rn);
+      n_lm = ld2f(m.lm, rn);
+      n_mu = ld2f(m.mu, rn);
+      n_b = ld2f(m.b, rn - 2 * ld2n);
+    }
     const bool row_mine = j >= xs && j < xe;  // warp-uniform
     const float tr_j = taper_axis_f(c.taper_table, c.g.np, gx0 + j, gnx),
                 tr_x = taper_axis_f(c.taper_table, c.g.np, gx0 + j - 2, gnx);

@@ -942,8 +942,27 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   const int batch = 1 + (int)batch_followers_.size();
   if (fp32_) {
     if (slab_) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
-    fc.strip = fused_strip_ > 0 ? fused_strip_ : fused_auto_strip(fc.n_zwarps, batch);
     const int wpb = 4;
+    if (fused_strip_ > 0) {
+      fc.strip = fused_strip_;
+    } else {  // whole waves of resident blocks, as fused_auto_strip does for variant 2
+      if (fused32_resident_ == 0) {
+        int per_sm = 0, sms = 0;
+        PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused32_step_kernel<MODE_PLAIN>, 128, 0));
+        PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+        fused32_resident_ = std::max(1, per_sm * sms);
+      }
+      const int blocks_x = ((fc.n_zwarps + wpb - 1) / wpb) * batch;
+      fc.strip = 8;
+      for (int waves = 1;; ++waves) {
+        const int n_strips = std::max(1, waves * fused32_resident_ / blocks_x);
+        const int st = (c.nx + n_strips - 1) / n_strips;
+        if (st <= 64 || n_strips >= c.nx) {
+          fc.strip = std::max(st, 2);
+          break;
+        }
+      }
+    }
     dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
     const FusedModel32 *m32 = fused_model32_.as<FusedModel32>();
     if (mode == MODE_SNAPSHOT) fused32_step_kernel<MODE_SNAPSHOT><<<grid, 128, 0, stream_>>>(fc, m32);

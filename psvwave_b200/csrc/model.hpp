@@ -230,6 +230,7 @@ class Model {
   DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_;  // receivers bucketed by grid row (fused.cuh)
   // optional FP32 wavefield mode (fused32.cuh): float images of the state and of lm mu b
   bool fp32_ = false;
+  int fused32_resident_ = 0;
   DeviceBuffer fields32_, medium32_, fused_model32_;
   GridArray conv_;  // double image of one float grid array (getters)
   DeviceBuffer fused_model_;                             // FusedModel per batch member (device copy of the pointers)
