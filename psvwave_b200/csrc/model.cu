@@ -8,6 +8,7 @@
 #include <iomanip>
 #include <iostream>
 #include <limits>
+#include <type_traits>
 #include <sstream>
 
 #include "fused.cuh"
@@ -339,6 +340,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
   l2_mode_ = o.l2_mode_;
+  coop_stages_ = o.coop_stages_;
   fp32_ = o.fp32_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
@@ -778,6 +780,16 @@ void Model::win_geometry(int batch, int *tiles, int *strip) {
 // Launch geometry of variant 3: CTAs per row, and rows per CTA such that the launch is a whole
 // number of waves of resident CTAs.
 namespace {
+// compiled consumer-warp counts of variant 3
+template <class F>
+auto with_pipe_warps(int nw, F &&f) {
+  switch (nw) {
+    case 12: return f(std::integral_constant<int, 12>{});
+    case 8: return f(std::integral_constant<int, 8>{});
+    case 4: return f(std::integral_constant<int, 4>{});
+    default: return f(std::integral_constant<int, 3>{});
+  }
+}
 template <int NW>
 int pipe_occupancy(size_t smem) {
   int per_sm = 0;
@@ -810,12 +822,13 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
   const int nw = pipe_warps();
   const int owned = nw * kFusedOwnedPairs;
   *tiles = (ld_ / 2 + owned - 1) / owned;
-  *smem = nw == 8 ? pipe_smem_bytes<8>(pipe_stages_) : nw == 4 ? pipe_smem_bytes<4>(pipe_stages_)
-                                                                 : pipe_smem_bytes<3>(pipe_stages_);
+  const int st = pipe_stages_;
+  *smem = with_pipe_warps(nw, [&](auto w) { return pipe_smem_bytes<decltype(w)::value>(st); });
+  if (*smem > kMaxPipeSmem) throw invalid_argument("pipe_stages: the ring does not fit in shared memory");
   if (pipe_resident_ == 0) {
     int sms = 0;
-    const int per_sm = nw == 8 ? pipe_occupancy<8>(*smem) : nw == 4 ? pipe_occupancy<4>(*smem)
-                                                                      : pipe_occupancy<3>(*smem);
+    const size_t sm = *smem;
+    const int per_sm = with_pipe_warps(nw, [&](auto w) { return pipe_occupancy<decltype(w)::value>(sm); });
     PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
     pipe_resident_ = std::max(1, per_sm * sms);
   }
@@ -832,6 +845,55 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
       // small grids are bound by the serial latency of a CTA's march (~1 us per row), so short strips
       // win although each recomputes 4 halo rows: 250x150, one model: 15.3 -> 10.2 us per step with 2 rows
       *strip = std::max(st, 2);
+      return;
+    }
+  }
+}
+
+// ---- variant 6: variant 3 without a producer warp, 12 marching warps per CTA (fused.cuh) --------
+namespace {
+constexpr int kCoopWarps = 12;
+template <class M, int MODE>
+void launch_coop_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem, cudaStream_t st) {
+  static size_t configured = 0;  // per instantiation
+  if (configured < smem) {
+    PSV_CUDA(cudaFuncSetAttribute(fused_coop_kernel<M, MODE, kCoopWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    configured = smem;
+  }
+  fused_coop_kernel<M, MODE, kCoopWarps><<<grid, kCoopWarps * 32, smem, st>>>(fc, models, stages);
+}
+template <class M>
+void launch_coop(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
+                 cudaStream_t st) {
+  if (mode == MODE_SNAPSHOT) launch_coop_k<M, MODE_SNAPSHOT>(fc, models, grid, stages, smem, st);
+  else if (mode == MODE_ACCUMULATE) launch_coop_k<M, MODE_ACCUMULATE>(fc, models, grid, stages, smem, st);
+  else launch_coop_k<M, MODE_PLAIN>(fc, models, grid, stages, smem, st);
+}
+}  // namespace
+
+// Launch geometry of variant 6: one CTA per SM (its ring fills the shared memory), whole waves.
+void Model::coop_geometry(int batch, int mode, int *tiles, int *strip, int *stages, size_t *smem) {
+  const int owned = kCoopWarps * kFusedOwnedPairs;
+  *tiles = (ld_ / 2 + owned - 1) / owned;
+  const int arrays = mode == MODE_ACCUMULATE ? kPipeArraysCorr : kPipeArrays;
+  int st = coop_stages_;
+  while (st > 2 && pipe_smem_bytes<kCoopWarps>(st, arrays) > kMaxPipeSmem) --st;
+  *stages = st;
+  *smem = pipe_smem_bytes<kCoopWarps>(st, arrays);
+  if (fused_strip_ > 0) {
+    *strip = fused_strip_;
+    return;
+  }
+  int sms = 0;
+  PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+  const int blocks_x = *tiles * batch;
+  const int nx = cfg_.nx;
+  for (int waves = 1;; ++waves) {
+    const int n_strips = std::max(1, waves * sms / blocks_x);
+    const int s = (nx + n_strips - 1) / n_strips;
+    if (s <= 128 || n_strips >= nx) {
+      *strip = std::max(s, 2);
       return;
     }
   }
@@ -906,8 +968,8 @@ void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, si
 
 void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
   const Config &c = cfg_;
-  if (slab_ && variant_ != 2 && variant_ != 3)
-    throw invalid_argument("A slab of a split grid runs the fused variants 2 and 3 only.");
+  if (slab_ && variant_ != 2 && variant_ != 3 && variant_ != 6)
+    throw invalid_argument("A slab of a split grid runs the fused variants 2, 3 and 6 only.");
   FusedCommon fc{};
   fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, x_off_, nx_global_};
   fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
@@ -979,6 +1041,14 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     if (exact_) launch_pair<ExactMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
     else launch_pair<FastMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
     ++stat_pair_launches_;
+  } else if (variant_ == 6) {
+    int tiles = 0, strip = 0, stages = 0;
+    size_t smem = 0;
+    coop_geometry(batch, mode, &tiles, &strip, &stages, &smem);
+    fc.strip = strip;
+    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
+    if (exact_) launch_coop<ExactMath>(mode, fc, models, grid, stages, smem, stream_);
+    else launch_coop<FastMath>(mode, fc, models, grid, stages, smem, stream_);
   } else if (variant_ == 4) {
     int tiles = 0, strip = 0;
     win_geometry(batch, &tiles, &strip);
@@ -995,21 +1065,18 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     const int nw = pipe_warps();
     int stages = pipe_stages_;
     if (mode == MODE_ACCUMULATE) {
-      stages = nw == 8 ? pipe_corr_stages<8>(stages) : nw == 4 ? pipe_corr_stages<4>(stages) : pipe_corr_stages<3>(stages);
-      smem = nw == 8   ? pipe_smem_bytes<8>(stages, kPipeArraysCorr)
-             : nw == 4 ? pipe_smem_bytes<4>(stages, kPipeArraysCorr)
-                       : pipe_smem_bytes<3>(stages, kPipeArraysCorr);
+      stages = with_pipe_warps(nw, [&](auto w) { return pipe_corr_stages<decltype(w)::value>(stages); });
+      const int sc = stages;
+      smem = with_pipe_warps(nw, [&](auto w) { return pipe_smem_bytes<decltype(w)::value>(sc, kPipeArraysCorr); });
     }
-    if (nw == 8) {
-      if (exact_) launch_pipe_m<ExactMath, 8>(mode, fc, models, grid, stages, smem, stream_);
-      else launch_pipe_m<FastMath, 8>(mode, fc, models, grid, stages, smem, stream_);
-    } else if (nw == 4) {
-      if (exact_) launch_pipe_m<ExactMath, 4>(mode, fc, models, grid, stages, smem, stream_);
-      else launch_pipe_m<FastMath, 4>(mode, fc, models, grid, stages, smem, stream_);
-    } else {
-      if (exact_) launch_pipe_m<ExactMath, 3>(mode, fc, models, grid, stages, smem, stream_);
-      else launch_pipe_m<FastMath, 3>(mode, fc, models, grid, stages, smem, stream_);
-    }
+    const int sl = stages;
+    const size_t sb = smem;
+    with_pipe_warps(nw, [&](auto w) {
+      constexpr int NW = decltype(w)::value;
+      if (exact_) launch_pipe_m<ExactMath, NW>(mode, fc, models, grid, sl, sb, stream_);
+      else launch_pipe_m<FastMath, NW>(mode, fc, models, grid, sl, sb, stream_);
+      return 0;
+    });
   } else {
     const int wpb = fused_block_ / 32;
     dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
@@ -1226,7 +1293,8 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
 void Model::march_begin(int i_shot, bool adjoint, bool store_fields) {
   check_shot(i_shot);
   bind();
-  if (variant_ != 2 && variant_ != 3) throw invalid_argument("psv_march_* needs the fused variant 2 or 3.");
+  if (variant_ != 2 && variant_ != 3 && variant_ != 6)
+    throw invalid_argument("psv_march_* needs the fused variant 2, 3 or 6.");
   if (march_.active) throw state_error("A march is already in progress on this model.");
   if (adjoint && snapshots_[i_shot].empty())
     throw state_error("The adjoint march needs the forward wavefield of this shot: run the stored forward march first.");
@@ -1979,6 +2047,9 @@ void Model::set_option(const std::string &name, long long v) {
       if (fp32_) ensure_fp32();
       zero_dynamic_fields();
     }
+  } else if (name == "coop_stages") {
+    if (v < 2 || v > 8) throw invalid_argument("coop_stages must be 2..8");
+    coop_stages_ = (int)v;
   } else if (name == "l2_mode") {
     if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
     l2_mode_ = (int)v;
@@ -1987,7 +2058,8 @@ void Model::set_option(const std::string &name, long long v) {
     pipe_stages_ = (int)v;
     pipe_resident_ = 0;
   } else if (name == "pipe_warps") {
-    if (v != 0 && v != 3 && v != 4 && v != 8) throw invalid_argument("pipe_warps must be 0 (auto), 3, 4 or 8");
+    if (v != 0 && v != 3 && v != 4 && v != 8 && v != 12)
+      throw invalid_argument("pipe_warps must be 0 (auto), 3, 4, 8 or 12");
     pipe_warps_ = (int)v;
     pipe_resident_ = 0;
     pipe_resident_ = 0;

@@ -75,7 +75,7 @@ SlabSpec slab_partition(int nx_global, int rank, int nranks, int halo);
 
 class Model {
  public:
-  static constexpr int kVariantCount = 6;
+  static constexpr int kVariantCount = 7;
   explicit Model(Config cfg, int device, const SlabSpec *slab = nullptr);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -183,6 +183,7 @@ class Model {
   void win_geometry(int batch, int *tiles, int *strip);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
   void pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem);
+  void coop_geometry(int batch, int mode, int *tiles, int *strip, int *stages, size_t *smem);
   // Slack (in doubles) before and after the snapshot and Lame-kernel allocations: the bulk copies of
   // the correlation launches read whole row segments, which start 2 pairs before a row and may run
   // past its end by a tile's tail.
@@ -252,6 +253,7 @@ class Model {
   int fused_resident_blocks_ = 0;
   int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
   int win_config_ = 0, win_resident_ = 0;
+  int coop_stages_ = 5;  // ring depth of variant 6
   int l2_mode_ = 0;  // L2 eviction hints of the variant-3 bulk copies (fused.cuh)
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;

@@ -45,7 +45,9 @@ VARIANTS = [dict(variant=0, exact=1), dict(variant=0, exact=0), dict(variant=1, 
             dict(variant=4, exact=1, win_config=2), dict(variant=4, exact=1, win_config=3, fused_strip=9),
             dict(variant=4, exact=1, win_config=4, fused_strip=13), dict(variant=4, exact=1, win_config=5),
             dict(variant=5, exact=1), dict(variant=5, exact=0), dict(variant=5, exact=1, pair_warps=4),
-            dict(variant=5, exact=1, pair_strip=9), dict(variant=5, exact=1, pair_stages=2, pair_strip=30)]
+            dict(variant=5, exact=1, pair_strip=9), dict(variant=5, exact=1, pair_stages=2, pair_strip=30),
+            dict(variant=6, exact=1), dict(variant=6, exact=0), dict(variant=6, exact=1, coop_stages=2, fused_strip=7),
+            dict(variant=6, exact=1, coop_stages=3, fused_strip=40)]
 
 
 def variant_id(o):
