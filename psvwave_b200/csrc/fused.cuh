@@ -241,7 +241,12 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
   double2 xz_m3 = zero2, xz_m2 = zero2, xz_m1 = zero2;
   double2 zz_m2 = zero2, zz_m1 = zero2;
 
-#pragma unroll 1
+#ifndef PSV_MARCH_UNROLL
+#define PSV_MARCH_UNROLL 1
+#endif
+#define PSV_PRAGMA_(x) _Pragma(#x)
+#define PSV_UNROLL_(n) PSV_PRAGMA_(unroll n)
+  PSV_UNROLL_(PSV_MARCH_UNROLL)
   for (; j < xe + 2; ++j, r += ld2n) {
     RowData d;
     rows.fetch(j, r, d);
