@@ -128,8 +128,15 @@ void Model::allocate() {
   guard_ = 6 * (size_t)ld_ + 1024;  // fused.cuh reads rows -4..nx+3 and up to 30 pairs past a row end
   n_snap_alloc_ = (c.nt + c.snapshot_interval - 1) / c.snapshot_interval;
 
-  GridArray *grids[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  GridArray *grids[] = {&vp_, &vs_, &rho_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (GridArray *g : grids) *g = make_grid();
+  // lm, mu, b -- what the step kernel re-reads every time step -- share one allocation
+  medium_.allocate(3 * (grid_elems_ + 2 * guard_) * sizeof(double));
+  GridArray *med[] = {&lm_, &mu_, &b_};
+  for (int k = 0; k < 3; ++k) {
+    med[k]->guard = guard_;
+    med[k]->view = medium_.as<double>() + (size_t)k * (grid_elems_ + 2 * guard_) + guard_;
+  }
   // the ten state arrays (2 buffers x vx vz txx tzz txz) sit in ONE allocation at a constant stride
   field_stride_ = grid_elems_ + 2 * guard_;
   fields_.allocate(10 * field_stride_ * sizeof(double));
@@ -348,10 +355,10 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
     if (dst.bytes() != src.bytes()) dst.allocate(src.bytes());
     copy_sync(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice);
   };
-  const GridArray *gs[] = {&o.vp_, &o.vs_, &o.rho_, &o.lm_, &o.mu_, &o.b_, &o.vp_kernel_, &o.vs_kernel_,
-                           &o.density_v_kernel_};
-  GridArray *gd[] = {&vp_, &vs_, &rho_, &lm_, &mu_, &b_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+  const GridArray *gs[] = {&o.vp_, &o.vs_, &o.rho_, &o.vp_kernel_, &o.vs_kernel_, &o.density_v_kernel_};
+  GridArray *gd[] = {&vp_, &vs_, &rho_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
   for (size_t i = 0; i < sizeof(gs) / sizeof(gs[0]); ++i) dcopy(gs[i]->buf, gd[i]->buf);
+  dcopy(o.medium_, medium_);
   cur_ = o.cur_;
   dcopy(o.fields_, fields_);
   dcopy(o.fields32_, fields32_);
@@ -597,6 +604,29 @@ void Model::fused_begin(int i_shot, int point_mode) {
     if (fused_model32_.bytes() < b32) fused_model32_.allocate(b32);
     copy_sync(fused_model32_.as<FusedModel32>(), f32.data(), b32, cudaMemcpyHostToDevice);
   }
+}
+
+// Persisting-L2 window over [lm | mu | b]: a carve-out of the 126 MB L2 keeps (a fraction of) the medium
+// resident across the launches of a time loop, the rest of the window streams.
+void Model::apply_l2_window() {
+  bind();
+  cudaStreamAttrValue attr{};
+  if (l2_persist_mb_ > 0) {
+    int max_persist = 0, max_window = 0;
+    PSV_CUDA(cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device_));
+    PSV_CUDA(cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device_));
+    const size_t want = std::min<size_t>((size_t)l2_persist_mb_ << 20, (size_t)max_persist);
+    PSV_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want));
+    const size_t bytes = std::min<size_t>(medium_.bytes(), (size_t)max_window);
+    attr.accessPolicyWindow.base_ptr = medium_.as<char>();
+    attr.accessPolicyWindow.num_bytes = bytes;
+    attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)bytes);
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  } else {
+    attr.accessPolicyWindow.num_bytes = 0;
+  }
+  PSV_CUDA(cudaStreamSetAttribute(stream_, cudaStreamAttributeAccessPolicyWindow, &attr));
 }
 
 // ---- optional FP32 wavefield mode (fused32.cuh) -----------------------------------------------
@@ -2050,6 +2080,10 @@ void Model::set_option(const std::string &name, long long v) {
   } else if (name == "coop_stages") {
     if (v < 2 || v > 8) throw invalid_argument("coop_stages must be 2..8");
     coop_stages_ = (int)v;
+  } else if (name == "l2_persist_mb") {
+    if (v < 0 || v > 120) throw invalid_argument("l2_persist_mb must be 0..120");
+    l2_persist_mb_ = (int)v;
+    apply_l2_window();
   } else if (name == "l2_mode") {
     if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
     l2_mode_ = (int)v;
@@ -2097,6 +2131,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
+  if (name == "l2_persist_mb") return l2_persist_mb_;
   if (name == "fp32") return fp32_ ? 1 : 0;
   if (name == "pair_warps") return pair_warps_;
   if (name == "pair_stages") return pair_stages_;

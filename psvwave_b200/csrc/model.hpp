@@ -61,7 +61,8 @@ class DeviceBuffer {
 // A pitched (nx, ld) grid array with its guard bands; data() points at element (0, 0).
 struct GridArray {
   DeviceBuffer buf;
-  double *data() const { return buf.as<double>() + guard; }
+  double *view = nullptr;  // set instead of `buf` when the array lives inside a shared allocation
+  double *data() const { return view ? view : buf.as<double>() + guard; }
   size_t guard = 0;
 };
 
@@ -216,7 +217,8 @@ class Model {
   DeviceBuffer fields_;                       // dynamic fields [2 buffers][vx vz txx tzz txz], each padded grid
   size_t field_stride_ = 0;                   // doubles between consecutive state arrays
   int cur_ = 0;                               // which buffer holds the current state
-  GridArray vp_, vs_, rho_, lm_, mu_, b_;     // medium
+  GridArray vp_, vs_, rho_, lm_, mu_, b_;     // medium (lm mu b: views into medium_, one L2 policy window)
+  DeviceBuffer medium_;                       // [lm | mu | b], each a padded grid
   DeviceBuffer lame_kernels_;                 // [lambda | mu | density_l], each nx*ld
   GridArray vp_kernel_, vs_kernel_, density_v_kernel_;
   DeviceBuffer taper_table_;                  // np_boundary + 1 values
@@ -254,6 +256,8 @@ class Model {
   int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
   int win_config_ = 0, win_resident_ = 0;
   int coop_stages_ = 5;  // ring depth of variant 6
+  int l2_persist_mb_ = 0;  // persisting-L2 carve-out for the medium arrays the step kernel re-reads (0 = off)
+  void apply_l2_window();
   int l2_mode_ = 0;  // L2 eviction hints of the variant-3 bulk copies (fused.cuh)
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;
