@@ -20,8 +20,13 @@ def pytest_configure(config):
 def pytest_collection_modifyitems(config, items):
     # GPU tests are selected with `-m gpu`; when they are collected on a box without a
     # device (plain `pytest tests/`), skip them instead of failing.
+    # A missing/broken extension is NOT a reason to skip: the GPU tests then fail loudly on import
+    # (there is no CPU fallback to fall back to).
     try:
         import psvwave_b200
+    except ImportError:
+        return
+    try:
         have_gpu = psvwave_b200.device_count() > 0
     except Exception:
         have_gpu = False
