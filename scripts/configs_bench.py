@@ -85,6 +85,15 @@ def main():
         r.set_parameter_fields(*start)
         c1["cpu_reference"] = dict(cpu_times(r, obs), cores=bench.omp_threads(), build="g++ -O3 -fopenmp (reference Release flags)")
         r.map_kernels_to_velocity()
+        # 1-thread row: a fresh process so that OMP_NUM_THREADS takes effect
+        import subprocess
+        code = ("import sys,time; sys.path.insert(0,%r); from oracle import oracle; m=oracle.RefModel(%r); "
+                "t=time.perf_counter(); m.forward_simulate(0, False); print(m.nx*m.nz*m.nt/(time.perf_counter()-t))" % (ROOT, C1_INI))
+        out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, OMP_NUM_THREADS="1"), capture_output=True, text=True)
+        try:
+            c1["cpu_reference_1_thread"] = {"forward_nostore_updates_per_s": float(out.stdout.strip().splitlines()[-1])}
+        except Exception:
+            c1["cpu_reference_1_thread"] = {"error": out.stderr[-200:]}
     print(json.dumps(c1), flush=True)
     del g
 
