@@ -251,11 +251,19 @@ int psv_timer_start(psv_handle h);
 int psv_timer_stop(psv_handle h, double *milliseconds);
 
 /* Tuning / instrumentation knobs, by name.  Unknown names fail with PSV_ERR_INVALID_ARGUMENT.
- *   "variant"  0 = one-thread-per-point kernels, 1 = vectorised x-marching kernels (default)
- *   "exact"    1 = IEEE operation order of the reference (true divisions, no FMA): results
- *              are bit-identical to the reference build; 0 (default) = reciprocals + FMA
- *   "profile"  1 = record CUDA events around sampled stencil launches (see psv_get_stat)
- *   "strip", "block"   launch geometry of variant 1 */
+ *   "variant"  which step kernels run the time loop (results are the same):
+ *              0 one thread per point, two sweeps      1 x-marching two sweeps
+ *              2 one fused launch per time step        3 (default) the same, fed by a TMA bulk-copy ring
+ *              4 shared-memory window                  5 two time steps per launch
+ *              6 variant 3 with 12 marching warps and no producer warp
+ *   "exact"    1 = IEEE operation order of the reference (true divisions, no FMA): results are
+ *              bit-identical to the reference build; 0 (default) = reciprocals + FMA (<= 1e-10)
+ *   "fp32"     1 = optional single-precision wavefield mode (state, medium and snapshots in float,
+ *              seismograms and sensitivity kernels in double); stated tolerance 1e-3 relative L2
+ *   "profile"  1 = record CUDA events around sampled step launches (see psv_get_stat)
+ *   launch geometry (sweeps under profiles/): "strip" "block" (variants 0/1), "fused_strip"
+ *              "fused_block" (2), "pipe_warps" "pipe_stages" "l2_mode" "l2_persist_mb" (3),
+ *              "win_config" (4), "pair_warps" "pair_stages" "pair_strip" (5), "coop_stages" (6) */
 int psv_set_option(psv_handle h, const char *name, long long value);
 /* Number of sweep-kernel variants compiled into the library ("variant" < this). */
 int psv_variant_count(void);
