@@ -44,10 +44,11 @@ struct RowOp {
   int z;          // target column
   int field;      // 0 = vx, 1 = vz
   int source;     // row of stf
-  int pad;
+  int x;          // target row (local)
   double weight;  // moment entry (x0.25 where the reference does)
   double sign;    // +1 / -1
   double d4;      // dx^4 or dz^4
+  double rd4;     // 1 / d4 (default arithmetic multiplies, "exact" divides like the reference)
 };
 
 enum PointMode { POINT_NONE = 0, POINT_FORWARD = 1, POINT_ADJOINT = 2 };
@@ -80,9 +81,10 @@ struct FusedCommon {
   // point operations
   int point_mode;
   int nt, it;
-  double dt, dxdz;
+  double dt, dxdz, rdxdz;  // rdxdz = 1 / (dx*dz), default arithmetic only
   const int *rec_row_start;  // [nx+1] CSR over rows of the receivers sorted by (ix, r)
   const int *rec_z;          // column of sorted receiver q
+  const int *rec_x;          // row of sorted receiver q
   const int *rec_id;         // original receiver number of sorted receiver q
   const int *op_row_start;   // [nx+1] CSR over rows of this shot's injection operations
   const RowOp *ops;
@@ -220,12 +222,21 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
   const bool zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
   const double tza = taper_axis(c.taper_table, c.g.np, z0, nz), tzb = taper_axis(c.taper_table, c.g.np, z0 + 1, nz);
 
-  // point operations present in this strip?
-  bool strip_rec = false, strip_ops = false;
-  if (c.point_mode != POINT_NONE) {
-    strip_rec = c.rec_row_start[xe] > c.rec_row_start[xs];
-    if (c.point_mode == POINT_FORWARD) strip_ops = c.op_row_start[xe] > c.op_row_start[xs];
+  // Cursors into the row-sorted point lists.  The row of the next receiver / injection operation sits in a
+  // register, so a row without point operations costs one compare instead of two dependent loads.
+  int rq = 0, rq_end = 0, oq = 0, oq_end = 0;
+  if (c.point_mode == POINT_FORWARD) {  // samples on the rows [mx0, mx1), injections on [xs, xe)
+    rq = c.rec_row_start[rg.mx0];
+    rq_end = c.rec_row_start[rg.mx1];
+    oq = c.op_row_start[xs];
+    oq_end = c.op_row_start[xe];
+  } else if (c.point_mode == POINT_ADJOINT) {  // adjoint sources on [xs, xe)
+    rq = c.rec_row_start[xs];
+    rq_end = c.rec_row_start[xe];
   }
+  constexpr int kNoRow = 0x7fffffff;
+  int rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
+  int op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
 
   // j = row whose stresses are updated in this iteration; velocities of row j-2 follow.
   int j = xs - 2;
@@ -286,14 +297,14 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         }
       }
       // receiver sampling from the old velocities (src/fdModel.cpp:576-596)
-      if (c.point_mode == POINT_FORWARD && strip_rec) {
-        const int q1 = c.rec_row_start[j + 1];
-        for (int q = c.rec_row_start[j]; q < q1; ++q) {
-          const int z = c.rec_z[q];
+      if (c.point_mode == POINT_FORWARD && j == rec_next) {
+        do {
+          const int z = c.rec_z[rq];
           if (mine && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + rg.it;
-            const double sx = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vx_0.y : vx_0.x), c.dxdz);
-            const double sz = __ddiv_rn(__dmul_rn(c.dt, (z & 1) ? vz_0.y : vz_0.x), c.dxdz);
+            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
+            const double pvx = (z & 1) ? vx_0.y : vx_0.x, pvz = (z & 1) ? vz_0.y : vz_0.x;
+            const double sx = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
+            const double sz = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
             if (rg.it == 0) {
               m.ux[t] = sx;
               m.uz[t] = sz;
@@ -302,7 +313,9 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
               m.uz[t] = __dadd_rn(m.uz[t - 1], sz);
             }
           }
-        }
+          ++rq;
+          rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
+        } while (rec_next == j);
       }
     }
 
@@ -371,14 +384,14 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         vz.y = ub ? bvz : vz.y;
       }
       // moment-tensor injection on the updated velocities (src/fdModel.cpp:681-751)
-      if (strip_ops) {
-        const int q1 = c.op_row_start[x + 1];
-        for (int q = c.op_row_start[x]; q < q1; ++q) {
-          const RowOp op = c.ops[q];
+      if (x == op_next) {
+        do {
+          const RowOp op = c.ops[oq];
           if (own && (op.z >> 1) == kp) {
             const double w = c.stf[(size_t)op.source * c.nt + rg.it];
             const double bb = (op.z & 1) ? b.y : b.x;
-            const double amp = __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(op.weight, w), c.dt), bb), op.d4);
+            const double amp = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(op.weight, w), c.dt), bb), op.d4)
+                                         : ((op.weight * w) * c.dt * bb) * op.rd4;
             const bool odd = op.z & 1;
             double t = op.field == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
             t = op.sign > 0 ? __dadd_rn(t, amp) : __dsub_rn(t, amp);
@@ -388,18 +401,21 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
               if (odd) vz.y = t; else vz.x = t;
             }
           }
-        }
+          ++oq;
+          op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
+        } while (op_next == x);
       }
       // adjoint-source injection at the receivers (src/fdModel.cpp:951-958)
-      if (c.point_mode == POINT_ADJOINT && strip_rec) {
-        const int q1 = c.rec_row_start[x + 1];
-        for (int q = c.rec_row_start[x]; q < q1; ++q) {
-          const int z = c.rec_z[q];
+      if (c.point_mode == POINT_ADJOINT && x == rec_next) {
+        do {
+          const int z = c.rec_z[rq];
           if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + rg.it;
+            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
             const double bb = (z & 1) ? b.y : b.x;
-            const double ax = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.ax[t]), c.dxdz);
-            const double az = __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.az[t]), c.dxdz);
+            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.ax[t]), c.dxdz)
+                                        : ((c.dt * bb) * m.ax[t]) * c.rdxdz;
+            const double az = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.az[t]), c.dxdz)
+                                        : ((c.dt * bb) * m.az[t]) * c.rdxdz;
             if (z & 1) {
               vx.y = __dadd_rn(vx.y, ax);
               vz.y = __dadd_rn(vz.y, az);
@@ -408,7 +424,9 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
               vz.x = __dadd_rn(vz.x, az);
             }
           }
-        }
+          ++rq;
+          rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
+        } while (rec_next == x);
       }
       sink.velocity(x, rv, vx, vz, b);
     }

@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
           if (own && (op.z >> 1) == kp) {
             const double w = c.stf[(size_t)op.source * c.nt + c.it];
             const double bb = (double)((op.z & 1) ? b.y : b.x);
-            const double amp = op.weight * w * c.dt * bb / op.d4;
+            const double amp = ((op.weight * w) * c.dt * bb) * op.rd4;
             const bool odd = op.z & 1;
             float &t = op.field == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
             t = (float)(op.sign > 0 ? (double)t + amp : (double)t - amp);
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
           if (own && (z >> 1) == kp) {
             const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
             const double bb = (double)((z & 1) ? b.y : b.x);
-            const double ax = c.dt * bb * m.ax[t] / c.dxdz, az = c.dt * bb * m.az[t] / c.dxdz;
+            const double ax = ((c.dt * bb) * m.ax[t]) * c.rdxdz, az = ((c.dt * bb) * m.az[t]) * c.rdxdz;
             if (z & 1) {
               vx.y = (float)((double)vx.y + ax);
               vz.y = (float)((double)vz.y + az);

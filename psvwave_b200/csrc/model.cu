@@ -233,10 +233,14 @@ void Model::build_plans() {
                      [&](int a, int b) { return c.ix_receivers[a] < c.ix_receivers[b]; });
     for (int r : order) ++row_start[local_row(c.ix_receivers[r]) + 1];
     for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
+    std::vector<int> rx(std::max(c.nr, 1), 0);
     for (size_t q = 0; q < order.size(); ++q) {
       rz[q] = c.iz_receivers[order[q]];
       rid[q] = order[q];
+      rx[q] = local_row(c.ix_receivers[order[q]]);
     }
+    rec_row_x_.allocate(rx.size() * sizeof(int));
+    copy_sync(rec_row_x_.as<int>(), rx.data(), rx.size() * sizeof(int), cudaMemcpyHostToDevice);
     rec_row_start_.allocate(row_start.size() * sizeof(int));
     rec_row_z_.allocate(rz.size() * sizeof(int));
     rec_row_id_.allocate(rid.size() * sizeof(int));
@@ -297,7 +301,7 @@ void Model::build_plans() {
       for (size_t q = 0; q < ops.size(); ++q) {
         const InjectOp &o = ops[order[q]];
         ++row_start[row_of(order[q]) + 1];
-        rops[q] = RowOp{o.point % ld_, o.field, o.source, 0, o.weight, o.sign, o.d4};
+        rops[q] = RowOp{o.point % ld_, o.field, o.source, o.point / ld_, o.weight, o.sign, o.d4, 1.0 / o.d4};
       }
       for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
       p.row_ops.allocate(rops.size() * sizeof(RowOp));
@@ -1024,8 +1028,10 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.it = it;
   fc.dt = c.dt;
   fc.dxdz = c.dx * c.dz;
+  fc.rdxdz = 1.0 / (c.dx * c.dz);
   fc.rec_row_start = rec_row_start_.as<int>();
   fc.rec_z = rec_row_z_.as<int>();
+  fc.rec_x = rec_row_x_.as<int>();
   fc.rec_id = rec_row_id_.as<int>();
   fc.op_row_start = plans_[i_shot].op_row_start.as<int>();
   fc.ops = plans_[i_shot].row_ops.as<RowOp>();

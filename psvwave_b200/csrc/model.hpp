@@ -230,7 +230,7 @@ class Model {
   DeviceBuffer rtf_ux_, rtf_uz_, obs_ux_, obs_uz_, a_stf_ux_, a_stf_uz_;  // [n_shots][nr][nt]
   DeviceBuffer rec_index_, rec_next_, rec_heads_;
   int n_rec_heads_ = 0;
-  DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_;  // receivers bucketed by grid row (fused.cuh)
+  DeviceBuffer rec_row_start_, rec_row_z_, rec_row_id_, rec_row_x_;  // receivers bucketed by grid row (fused.cuh)
   // optional FP32 wavefield mode (fused32.cuh): float images of the state and of lm mu b
   bool fp32_ = false;
   int fused32_resident_ = 0;
