@@ -70,6 +70,7 @@ struct FusedCommon {
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
   int tile_pairs;   // variant 5: z-pairs per CTA tile
+  int rec_increments;  // 1: receiver samples are stored as increments, the running sum follows the time loop
   int l2_mode;      // variant 3: bit 0 = medium rows evict_last in L2, bit 1 = state rows evict_first
   int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
   size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
@@ -305,7 +306,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
             const double pvx = (z & 1) ? vx_0.y : vx_0.x, pvz = (z & 1) ? vz_0.y : vz_0.x;
             const double sx = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
             const double sz = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
-            if (rg.it == 0) {
+            if (c.rec_increments || rg.it == 0) {  // (no read-modify-write of global memory inside the march)
               m.ux[t] = sx;
               m.uz[t] = sz;
             } else {

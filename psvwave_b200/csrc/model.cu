@@ -1015,6 +1015,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.tile_pairs = 0;
   fc.it_step = 0;
   fc.l2_mode = l2_mode_;
+  fc.rec_increments = receiver_increments() ? 1 : 0;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
   // free window in local rows; a slab correlates only on the rows it owns
@@ -1167,6 +1168,19 @@ struct Profiler {  // CUDA events around sampled sweep launches
 };
 }  // namespace
 
+// The fused FP64 marches (variants 2, 3, 5, 6) store receiver increments; the running sum over time
+// is taken once after the time loop (same order, same rounding as the reference's in-loop sum).
+bool Model::receiver_increments() const { return !fp32_ && variant_ >= 2 && variant_ != 4; }
+
+void Model::finish_receivers(int i_shot, cudaStream_t st) {
+  const Config &c = cfg_;
+  if (c.nr == 0 || c.nt == 0) return;
+  const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
+  receiver_prefix_kernel<<<blocks_for(2 * (size_t)c.nr, 64), 64, 0, st>>>(rtf_ux_.as<>() + shot_rows,
+                                                                         rtf_uz_.as<>() + shot_rows, c.nr, c.nt);
+  PSV_CUDA(cudaGetLastError());
+}
+
 // fdModel::forward_simulate (src/fdModel.cpp:526-787)
 void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool output_wavefields) {
   check_shot(i_shot);
@@ -1239,6 +1253,11 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
       ++stat_launches_;
     }
     if (output_wavefields && it % 10 == 0) write_wavefield_files(it);
+  }
+  if (receiver_increments()) {  // running sum of the stored increments, for every model of a batch
+    finish_receivers(i_shot, stream_);
+    for (Model *f : batch_followers_) f->finish_receivers(i_shot, stream_);
+    stat_launches_ += 1 + (long long)batch_followers_.size();
   }
   PSV_CUDA(cudaEventRecord(ev_end_, stream_));
   PSV_CUDA(cudaGetLastError());
@@ -1376,6 +1395,10 @@ void Model::march_end() {
   if (!march_.active) throw state_error("psv_march_end without psv_march_begin.");
   bind();
   march_.active = false;
+  if (!march_.adjoint && receiver_increments()) {
+    finish_receivers(march_.i_shot, stream_);
+    ++stat_launches_;
+  }
   PSV_CUDA(cudaEventRecord(ev_end_, stream_));
   PSV_CUDA(cudaStreamSynchronize(stream_));
   float ms = 0;

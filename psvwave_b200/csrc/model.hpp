@@ -169,6 +169,8 @@ class Model {
   void launch_velocity(double sdt);
   // variant 2: one fused launch per time step (fused.cuh)
   void fused_begin(int i_shot, int point_mode);
+  bool receiver_increments() const;
+  void finish_receivers(int i_shot, cudaStream_t st);
   void fill_fused_model(int i_shot, void *out) const;
   void fill_fused_model32(int i_shot, void *out) const;
   void ensure_fp32();

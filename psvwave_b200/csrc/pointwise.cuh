@@ -34,6 +34,20 @@ __global__ void record_receivers_kernel(const RecordArgs a) {
   }
 }
 
+// Running sum of src/fdModel.cpp:584-594 over the increments dt*v/(dx*dz) the fused step kernels
+// stored: u[it] = u[it-1] + s[it], one thread per trace, the reference's sequential order and
+// rounding (bit-identical to summing inside the time loop).
+__global__ void receiver_prefix_kernel(double *ux, double *uz, int nr, int nt) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= 2 * nr) return;
+  double *u = (r < nr ? ux : uz) + (size_t)(r % nr) * nt;
+  double acc = u[0];
+  for (int it = 1; it < nt; ++it) {
+    acc = __dadd_rn(acc, u[it]);
+    u[it] = acc;
+  }
+}
+
 // ---- moment-tensor source injection (src/fdModel.cpp:681-751) ------------------------------
 // The host flattens the shot's sources into point operations in the reference's order
 // (source list order, then the 12 updates of a source in the order they are written) and
