@@ -238,6 +238,13 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
   constexpr int kNoRow = 0x7fffffff;
   int rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
   int op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
+  // adjoint sources of the next receiver, fetched when the cursor moves (rows ahead of their use)
+  double nax = 0.0, naz = 0.0;
+  if (c.point_mode == POINT_ADJOINT && rq < rq_end) {
+    const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
+    nax = m.ax[t];
+    naz = m.az[t];
+  }
 
   // j = row whose stresses are updated in this iteration; velocities of row j-2 follow.
   int j = xs - 2;
@@ -411,12 +418,11 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
         do {
           const int z = c.rec_z[rq];
           if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
             const double bb = (z & 1) ? b.y : b.x;
-            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.ax[t]), c.dxdz)
-                                        : ((c.dt * bb) * m.ax[t]) * c.rdxdz;
-            const double az = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), m.az[t]), c.dxdz)
-                                        : ((c.dt * bb) * m.az[t]) * c.rdxdz;
+            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), nax), c.dxdz)
+                                        : ((c.dt * bb) * nax) * c.rdxdz;
+            const double az = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), naz), c.dxdz)
+                                        : ((c.dt * bb) * naz) * c.rdxdz;
             if (z & 1) {
               vx.y = __dadd_rn(vx.y, ax);
               vz.y = __dadd_rn(vz.y, az);
@@ -426,7 +432,13 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
             }
           }
           ++rq;
-          rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
+          rec_next = kNoRow;
+          if (rq < rq_end) {
+            rec_next = c.rec_x[rq];
+            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
+            nax = m.ax[t];
+            naz = m.az[t];
+          }
         } while (rec_next == x);
       }
       sink.velocity(x, rv, vx, vz, b);
