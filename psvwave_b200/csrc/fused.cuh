@@ -393,23 +393,42 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       }
       // moment-tensor injection on the updated velocities (src/fdModel.cpp:681-751)
       if (x == op_next) {
+        // The operations of this row are fetched by the lanes in parallel (lane l takes operation oq + l and its
+        // source-time-function sample: two global round trips for the whole row instead of two per operation),
+        // then applied one after the other in list order by the lane that owns each target point.
         do {
-          const RowOp op = c.ops[oq];
-          if (own && (op.z >> 1) == kp) {
-            const double w = c.stf[(size_t)op.source * c.nt + rg.it];
-            const double bb = (op.z & 1) ? b.y : b.x;
-            const double amp = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(op.weight, w), c.dt), bb), op.d4)
-                                         : ((op.weight * w) * c.dt * bb) * op.rd4;
-            const bool odd = op.z & 1;
-            double t = op.field == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
-            t = op.sign > 0 ? __dadd_rn(t, amp) : __dsub_rn(t, amp);
-            if (op.field == 0) {
-              if (odd) vx.y = t; else vx.x = t;
-            } else {
-              if (odd) vz.y = t; else vz.x = t;
+          const int n = min(32, oq_end - oq);
+          int oz = 0, ofs = 0;
+          double base = 0.0, dd = 1.0;
+          bool valid = false;
+          if (lane < n) {
+            const RowOp op = c.ops[oq + lane];
+            valid = op.x == x;
+            if (valid) {
+              oz = op.z;
+              ofs = op.field | (op.sign > 0 ? 0 : 2);
+              base = __dmul_rn(__dmul_rn(op.weight, c.stf[(size_t)op.source * c.nt + rg.it]), c.dt);
+              dd = M::kExact ? op.d4 : op.rd4;
             }
           }
-          ++oq;
+          const int cnt = __popc(__ballot_sync(0xffffffffu, valid));  // the row's operations are a prefix
+          for (int l = 0; l < cnt; ++l) {
+            const int z = __shfl_sync(0xffffffffu, oz, l), fs = __shfl_sync(0xffffffffu, ofs, l);
+            const double ba = __shfl_sync(0xffffffffu, base, l), d = __shfl_sync(0xffffffffu, dd, l);
+            if (own && (z >> 1) == kp) {
+              const bool odd = z & 1;
+              const double bb = odd ? b.y : b.x;
+              const double amp = M::kExact ? __ddiv_rn(__dmul_rn(ba, bb), d) : (ba * bb) * d;
+              double t = (fs & 1) == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
+              t = (fs & 2) == 0 ? __dadd_rn(t, amp) : __dsub_rn(t, amp);
+              if ((fs & 1) == 0) {
+                if (odd) vx.y = t; else vx.x = t;
+              } else {
+                if (odd) vz.y = t; else vz.x = t;
+              }
+            }
+          }
+          oq += cnt;
           op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
         } while (op_next == x);
       }
