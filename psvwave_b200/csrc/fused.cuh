@@ -70,6 +70,7 @@ struct FusedCommon {
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
   int tile_pairs;   // variant 5: z-pairs per CTA tile
+  int pdl;             // variant 3: launched with programmatic stream serialization (see fused_pipe_kernel)
   int rec_increments;  // 1: receiver samples are stored as increments, the running sum follows the time loop
   int l2_mode;      // variant 3: bit 0 = medium rows evict_last in L2, bit 1 = state rows evict_first
   int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
@@ -658,6 +659,13 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  if (c.pdl) {
+    // Programmatic dependent launch: the next time step's CTAs may be scheduled (and set up their barriers) on
+    // SMs this launch has already left; everything that touches the wavefield -- this launch reads the state
+    // the previous one wrote and overwrites the state it read -- comes after the wait.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
 
   const FusedModel &m = models[blockIdx.z];
   const long long ld2n = c.g.ld >> 1;
@@ -822,6 +830,20 @@ __global__ void __launch_bounds__(NW * 32) fused_coop_kernel(const FusedCommon c
   GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
                   m.f[c.parity ^ 1][4], xs, xe, own};
   fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xs, xe, xs, xe, own, own, c.it});
+}
+
+// Running sum of the receiver increments the marches stored (src/fdModel.cpp:584-594): u[it] = u[it-1] + s[it],
+// one thread per trace and model (blockIdx.y), the reference's sequential order and rounding.
+__global__ void receiver_prefix_models_kernel(const FusedModel *__restrict__ models, int nr, int nt) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= 2 * nr) return;
+  const FusedModel &m = models[blockIdx.y];
+  double *u = (r < nr ? m.ux : m.uz) + (size_t)(r % nr) * nt;
+  double acc = u[0];
+  for (int it = 1; it < nt; ++it) {
+    acc = __dadd_rn(acc, u[it]);
+    u[it] = acc;
+  }
 }
 
 }  // namespace psv

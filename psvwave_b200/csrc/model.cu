@@ -351,6 +351,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
   l2_mode_ = o.l2_mode_;
+  pdl_ = o.pdl_;
   coop_stages_ = o.coop_stages_;
   fp32_ = o.fp32_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
@@ -719,6 +720,20 @@ void launch_pipe_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, i
                                   (int)smem));
     configured = smem;
   }
+  if (fc.pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3((NW + 1) * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PSV_CUDA(cudaLaunchKernelEx(&cfg, fused_pipe_kernel<M, MODE, NW>, fc, models, stages));
+    return;
+  }
   fused_pipe_kernel<M, MODE, NW><<<grid, (NW + 1) * 32, smem, st>>>(fc, models, stages);
 }
 template <class M, int NW>
@@ -1015,6 +1030,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.tile_pairs = 0;
   fc.it_step = 0;
   fc.l2_mode = l2_mode_;
+  fc.pdl = (pdl_ && variant_ == 3 && !fp32_) ? 1 : 0;
   fc.rec_increments = receiver_increments() ? 1 : 0;
   fc.snap_field_stride = (size_t)n_snap_alloc_ * grid_elems_;
   fc.snap_offset = (size_t)snap * grid_elems_;
@@ -1254,10 +1270,12 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
     }
     if (output_wavefields && it % 10 == 0) write_wavefield_files(it);
   }
-  if (receiver_increments()) {  // running sum of the stored increments, for every model of a batch
-    finish_receivers(i_shot, stream_);
-    for (Model *f : batch_followers_) f->finish_receivers(i_shot, stream_);
-    stat_launches_ += 1 + (long long)batch_followers_.size();
+  if (receiver_increments() && c.nr > 0) {  // running sum of the stored increments, all models of a batch at once
+    const int n_models = 1 + (int)batch_followers_.size();
+    receiver_prefix_models_kernel<<<dim3(blocks_for(2 * (size_t)c.nr, 64), n_models), 64, 0, stream_>>>(
+        fused_model_.as<FusedModel>(), c.nr, c.nt);
+    PSV_CUDA(cudaGetLastError());
+    ++stat_launches_;
   }
   PSV_CUDA(cudaEventRecord(ev_end_, stream_));
   PSV_CUDA(cudaGetLastError());
@@ -2113,6 +2131,8 @@ void Model::set_option(const std::string &name, long long v) {
     if (v < 0 || v > 120) throw invalid_argument("l2_persist_mb must be 0..120");
     l2_persist_mb_ = (int)v;
     apply_l2_window();
+  } else if (name == "pdl") {
+    pdl_ = v != 0;
   } else if (name == "l2_mode") {
     if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
     l2_mode_ = (int)v;
@@ -2160,6 +2180,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
+  if (name == "pdl") return pdl_ ? 1 : 0;
   if (name == "l2_persist_mb") return l2_persist_mb_;
   if (name == "fp32") return fp32_ ? 1 : 0;
   if (name == "pair_warps") return pair_warps_;

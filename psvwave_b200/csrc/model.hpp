@@ -260,6 +260,7 @@ class Model {
   int coop_stages_ = 5;  // ring depth of variant 6
   int l2_persist_mb_ = 0;  // persisting-L2 carve-out for the medium arrays the step kernel re-reads (0 = off)
   void apply_l2_window();
+  bool pdl_ = false;  // programmatic dependent launch of consecutive variant-3 step kernels
   int l2_mode_ = 0;  // L2 eviction hints of the variant-3 bulk copies (fused.cuh)
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;
