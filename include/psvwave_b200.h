@@ -261,6 +261,10 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
  *   "fp32"     1 = optional single-precision wavefield mode (state, medium and snapshots in float,
  *              seismograms and sensitivity kernels in double); stated tolerance 1e-3 relative L2
  *   "profile"  1 = record CUDA events around sampled step launches (see psv_get_stat)
+ *   "graph"    the time loop of one (direction, shot, store) captured into a CUDA graph on first use and replayed
+ *              afterwards: 1 = always, 0 = never, -1 (default) = when a step launch covers at most 2^20 grid points
+ *              (the step kernel is then shorter than the gap between two stream launches); "graphs_cached" reads
+ *              the number of graphs held.  "pdl" 1 = programmatic dependent launch of consecutive variant-3 steps
  *   launch geometry (sweeps under profiles/): "strip" "block" (variants 0/1), "fused_strip"
  *              "fused_block" (2), "pipe_warps" "pipe_stages" "l2_mode" "l2_persist_mb" (3),
  *              "win_config" (4), "pair_warps" "pair_stages" "pair_strip" (5), "coop_stages" (6) */

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdint>
 #include <cstring>
 #include <fstream>
 #include <iomanip>
@@ -104,6 +105,8 @@ Model::Model(Config cfg, int device, const SlabSpec *slab) : cfg_(std::move(cfg)
 
 Model::~Model() {
   cudaSetDevice(device_);
+  for (auto &g : graphs_)
+    if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
   for (cudaEvent_t e : prof_events_) cudaEventDestroy(e);
   if (ev_begin_) cudaEventDestroy(ev_begin_);
   if (ev_end_) cudaEventDestroy(ev_end_);
@@ -352,6 +355,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   pipe_warps_ = o.pipe_warps_;
   l2_mode_ = o.l2_mode_;
   pdl_ = o.pdl_;
+  graph_ = o.graph_;
   coop_stages_ = o.coop_stages_;
   fp32_ = o.fp32_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
@@ -1197,6 +1201,77 @@ void Model::finish_receivers(int i_shot, cudaStream_t st) {
   PSV_CUDA(cudaGetLastError());
 }
 
+// ---- CUDA-graph replay of a time loop (option "graph") ----
+// Everything a captured launch bakes in (FusedCommon by value, the models pointer, the launch geometry) is a function
+// of the values below; what the kernels read through FusedModel (state, medium, snapshot and seismogram pointers) is
+// uploaded by fused_begin before every run and may change freely.
+std::vector<unsigned long long> Model::graph_key(int direction, int i_shot, bool store) const {
+  auto p = [](const void *q) { return (unsigned long long)(uintptr_t)q; };
+  auto n = [](long long v) { return (unsigned long long)v; };
+  const ShotPlan &plan = plans_[i_shot];
+  return {n(direction > 0), n(i_shot), n(store), n(variant_), n(exact_), n(fp32_), n(fused_strip_), n(fused_block_),
+          n(pipe_stages_), n(pipe_warps_), n(win_config_), n(coop_stages_), n(pdl_), n(l2_mode_), n(pair_warps_),
+          n(pair_stages_), n(pair_strip_), n((long long)batch_followers_.size()), p(fused_model_.as<char>()),
+          p(fused_model32_.as<char>()), p(fields_.as<char>()), n((long long)fields_.bytes()), p(fields32_.as<char>()),
+          n((long long)fields32_.bytes()), p(taper_table_.as<char>()), p(rec_row_start_.as<char>()),
+          p(rec_row_z_.as<char>()), p(rec_row_x_.as<char>()), p(rec_row_id_.as<char>()),
+          p(plan.op_row_start.as<char>()), p(plan.row_ops.as<char>()), p(stf_.as<char>()), n(n_snap_alloc_),
+          n(cfg_.nt), n(cfg_.snapshot_interval), n(cfg_.nr)};
+}
+
+// Replay pays when a step launch is shorter than the ~2.5 us a stream launch costs on top of a graph node: by default
+// for launches of up to 2^20 grid points (all models of an ensemble counted), and only while the graphs of all shots
+// and both directions fit the node budget of the cache.
+namespace {
+constexpr long long kGraphAutoPoints = 1 << 20;
+constexpr long long kGraphNodeBudget = 400000;
+}  // namespace
+
+bool Model::graph_wanted() const {
+  if (graph_ == 0 || variant_ < 2 || profile_ || slab_) return false;
+  if (graph_ == 1) return true;
+  const long long points = (long long)cfg_.nx * cfg_.nz * (1 + (long long)batch_followers_.size());
+  return points <= kGraphAutoPoints && 2LL * cfg_.n_shots * (cfg_.nt + 2) <= kGraphNodeBudget;
+}
+
+void Model::drop_graphs() {
+  for (auto &g : graphs_)
+    if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+  graphs_.clear();
+}
+
+void Model::graph_capture_begin() { PSV_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeRelaxed)); }
+
+void Model::graph_capture_abort() {
+  cudaGraph_t g = nullptr;
+  cudaStreamEndCapture(stream_, &g);
+  if (g) cudaGraphDestroy(g);
+  cudaGetLastError();
+}
+
+const Model::LoopGraph &Model::graph_capture_end(const std::vector<unsigned long long> &key) {
+  cudaGraph_t g = nullptr;
+  PSV_CUDA(cudaStreamEndCapture(stream_, &g));
+  LoopGraph lg;
+  const cudaError_t e = cudaGraphInstantiate(&lg.exec, g, 0);
+  cudaGraphDestroy(g);
+  PSV_CUDA(e);
+  lg.end_cur = cur_;
+  lg.launches = stat_launches_;
+  lg.pair_launches = stat_pair_launches_;
+  long long nodes = lg.launches;  // one graph holds a node per time step
+  for (const auto &o : graphs_) nodes += o.second.launches;
+  if (nodes > kGraphNodeBudget) drop_graphs();
+  return graphs_[key] = lg;
+}
+
+void Model::graph_replay(const LoopGraph &g) {
+  PSV_CUDA(cudaGraphLaunch(g.exec, stream_));
+  cur_ = g.end_cur;
+  stat_launches_ = g.launches;
+  stat_pair_launches_ = g.pair_launches;
+}
+
 // fdModel::forward_simulate (src/fdModel.cpp:526-787)
 void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool output_wavefields) {
   check_shot(i_shot);
@@ -1211,8 +1286,34 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
+  // option "graph": the loop of this (shot, store) is captured once, then replayed
+  const bool use_graph = graph_wanted() && !output_wavefields;
+  const LoopGraph *cached = nullptr;
+  std::vector<unsigned long long> gkey;
+  if (use_graph) {
+    fused_begin(i_shot, POINT_FORWARD);  // synchronous upload: outside the capture
+    gkey = graph_key(+1, i_shot, store_fields);
+    auto f = graphs_.find(gkey);
+    if (f != graphs_.end()) cached = &f->second;
+  }
+  if (cached) {
+    PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+    graph_replay(*cached);
+    PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+    PSV_CUDA(cudaStreamSynchronize(stream_));
+    float gms = 0;
+    PSV_CUDA(cudaEventElapsedTime(&gms, ev_begin_, ev_end_));
+    stat_elapsed_ms_ = gms;
+    if (verbose) {
+      const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+      std::cout << "Seconds elapsed for forward wave simulation: " << secs << std::endl;
+    }
+    return;
+  }
+  if (use_graph) graph_capture_begin();
+  try {
   zero_dynamic_fields();
-  PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+  if (!use_graph) PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
   Profiler prof(prof_events_, stream_, profile_, c.nt);
 
   const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
@@ -1222,7 +1323,7 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   InjectArgs ia{F(0), F(1), b_.data(), stf_.as<>(), plan.ops.as<InjectOp>(),
                 plan.heads.as<int>(), plan.n_heads, c.nt, 0, c.dt};
 
-  if (variant_ >= 2) fused_begin(i_shot, POINT_FORWARD);
+  if (variant_ >= 2 && !use_graph) fused_begin(i_shot, POINT_FORWARD);
   for (int it = 0; it < c.nt; ++it) {
     if (variant_ >= 2) {
       const bool snap = store_fields && it % c.snapshot_interval == 0;
@@ -1277,6 +1378,11 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
     PSV_CUDA(cudaGetLastError());
     ++stat_launches_;
   }
+  if (use_graph) {
+    const LoopGraph &lg = graph_capture_end(gkey);
+    PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+    graph_replay(lg);
+  }
   PSV_CUDA(cudaEventRecord(ev_end_, stream_));
   PSV_CUDA(cudaGetLastError());
   PSV_CUDA(cudaStreamSynchronize(stream_));
@@ -1284,6 +1390,10 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   PSV_CUDA(cudaEventElapsedTime(&ms, ev_begin_, ev_end_));
   stat_elapsed_ms_ = ms;
   prof.collect(stat_stress_ms_, stat_velocity_ms_);
+  } catch (...) {
+    if (use_graph) graph_capture_abort();
+    throw;
+  }
   if (verbose) {
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
     std::cout << "Seconds elapsed for forward wave simulation: " << secs << std::endl;
@@ -1305,15 +1415,41 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
+  const bool use_graph = graph_wanted();
+  const LoopGraph *cached = nullptr;
+  std::vector<unsigned long long> gkey;
+  if (use_graph) {
+    fused_begin(i_shot, POINT_ADJOINT);  // synchronous upload: outside the capture
+    gkey = graph_key(-1, i_shot, true);
+    gkey.push_back((unsigned long long)(uintptr_t)snapshots_[i_shot].as<char>());
+    auto f = graphs_.find(gkey);
+    if (f != graphs_.end()) cached = &f->second;
+  }
+  if (cached) {
+    PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+    graph_replay(*cached);
+    PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+    PSV_CUDA(cudaStreamSynchronize(stream_));
+    float gms = 0;
+    PSV_CUDA(cudaEventElapsedTime(&gms, ev_begin_, ev_end_));
+    stat_elapsed_ms_ = gms;
+    if (verbose) {
+      const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+      std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
+    }
+    return;
+  }
+  if (use_graph) graph_capture_begin();
+  try {
   zero_dynamic_fields();
-  PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+  if (!use_graph) PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
   Profiler prof(prof_events_, stream_, profile_, c.nt);
 
   const size_t shot_rows = (size_t)i_shot * c.nr * c.nt;
   AdjointInjectArgs aa{F(0), F(1), b_.data(), a_stf_ux_.as<>() + shot_rows,
                        a_stf_uz_.as<>() + shot_rows, rec_index_.as<int>(), rec_next_.as<int>(),
                        rec_heads_.as<int>(), n_rec_heads_, c.nt, 0, c.dt, c.dx * c.dz};
-  if (variant_ >= 2) fused_begin(i_shot, POINT_ADJOINT);
+  if (variant_ >= 2 && !use_graph) fused_begin(i_shot, POINT_ADJOINT);
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
     // variant 5 retreats two steps per launch unless the second one correlates with a snapshot
@@ -1345,6 +1481,11 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
       ++stat_launches_;
     }
   }
+  if (use_graph) {
+    const LoopGraph &lg = graph_capture_end(gkey);
+    PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+    graph_replay(lg);
+  }
   PSV_CUDA(cudaEventRecord(ev_end_, stream_));
   PSV_CUDA(cudaGetLastError());
   PSV_CUDA(cudaStreamSynchronize(stream_));
@@ -1352,6 +1493,10 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   PSV_CUDA(cudaEventElapsedTime(&ms, ev_begin_, ev_end_));
   stat_elapsed_ms_ = ms;
   prof.collect(stat_stress_ms_, stat_velocity_ms_);
+  } catch (...) {
+    if (use_graph) graph_capture_abort();
+    throw;
+  }
   if (verbose) {
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
     std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
@@ -2133,6 +2278,10 @@ void Model::set_option(const std::string &name, long long v) {
     apply_l2_window();
   } else if (name == "pdl") {
     pdl_ = v != 0;
+  } else if (name == "graph") {
+    if (v < -1 || v > 1) throw invalid_argument("graph must be -1 (auto), 0 or 1");
+    graph_ = (int)v;
+    if (graph_ == 0) drop_graphs();
   } else if (name == "l2_mode") {
     if (v < 0 || v > 3) throw invalid_argument("l2_mode must be 0..3");
     l2_mode_ = (int)v;
@@ -2181,6 +2330,8 @@ long long Model::get_option(const std::string &name) const {
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
   if (name == "pdl") return pdl_ ? 1 : 0;
+  if (name == "graph") return graph_;
+  if (name == "graphs_cached") return (long long)graphs_.size();
   if (name == "l2_persist_mb") return l2_persist_mb_;
   if (name == "fp32") return fp32_ ? 1 : 0;
   if (name == "pair_warps") return pair_warps_;

@@ -262,6 +262,22 @@ class Model {
   void apply_l2_window();
   bool pdl_ = false;  // programmatic dependent launch of consecutive variant-3 step kernels
   int l2_mode_ = 0;  // L2 eviction hints of the variant-3 bulk copies (fused.cuh)
+  // CUDA-graph replay of a whole time loop (option "graph"): a small grid's step kernel is shorter than the gap
+  // between two stream launches, so the loop of one (direction, shot, store) is captured once and replayed.
+  struct LoopGraph {
+    cudaGraphExec_t exec = nullptr;
+    int end_cur = 0;
+    long long launches = 0, pair_launches = 0;
+  };
+  int graph_ = -1;  // -1 = auto (small grids only, see graph_wanted), 0 = off, 1 = on
+  bool graph_wanted() const;
+  std::map<std::vector<unsigned long long>, LoopGraph> graphs_;
+  std::vector<unsigned long long> graph_key(int direction, int i_shot, bool store) const;
+  void graph_capture_begin();
+  void graph_capture_abort();
+  const LoopGraph &graph_capture_end(const std::vector<unsigned long long> &key);
+  void graph_replay(const LoopGraph &g);
+  void drop_graphs();
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;
   double stat_pair_ms_ = 0;
