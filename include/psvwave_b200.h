@@ -263,7 +263,8 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
  *   "profile"  1 = record CUDA events around sampled step launches (see psv_get_stat)
  *   "graph"    the time loop of one (direction, shot, store) captured into a CUDA graph on first use and replayed
  *              afterwards: 1 = always, 0 = never, -1 (default) = when a step launch covers at most 2^20 grid points
- *              (the step kernel is then shorter than the gap between two stream launches); "graphs_cached" reads
+ *              (the step kernel is then shorter than the gap between two stream launches) and the same loop is
+ *              run a second time; "graphs_cached" reads
  *              the number of graphs held.  "pdl" 1 = programmatic dependent launch of consecutive variant-3 steps
  *   launch geometry (sweeps under profiles/): "strip" "block" (variants 0/1), "fused_strip"
  *              "fused_block" (2), "pipe_warps" "pipe_stages" "l2_mode" "l2_persist_mb" (3),

@@ -1238,6 +1238,7 @@ void Model::drop_graphs() {
   for (auto &g : graphs_)
     if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
   graphs_.clear();
+  graph_seen_.clear();
 }
 
 void Model::graph_capture_begin() { PSV_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeRelaxed)); }
@@ -1287,7 +1288,8 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
   // option "graph": the loop of this (shot, store) is captured once, then replayed
-  const bool use_graph = graph_wanted() && !output_wavefields;
+  bool use_graph = graph_wanted() && !output_wavefields;
+  const bool begun = use_graph;
   const LoopGraph *cached = nullptr;
   std::vector<unsigned long long> gkey;
   if (use_graph) {
@@ -1295,6 +1297,9 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
     gkey = graph_key(+1, i_shot, store_fields);
     auto f = graphs_.find(gkey);
     if (f != graphs_.end()) cached = &f->second;
+    // auto mode: a loop seen for the first time is launched kernel by kernel (capture + instantiation cost about
+    // a third of a small march); it is captured when it comes back
+    else if (graph_ < 0 && graph_seen_[gkey]++ == 0) use_graph = false;
   }
   if (cached) {
     PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
@@ -1323,7 +1328,7 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   InjectArgs ia{F(0), F(1), b_.data(), stf_.as<>(), plan.ops.as<InjectOp>(),
                 plan.heads.as<int>(), plan.n_heads, c.nt, 0, c.dt};
 
-  if (variant_ >= 2 && !use_graph) fused_begin(i_shot, POINT_FORWARD);
+  if (variant_ >= 2 && !begun) fused_begin(i_shot, POINT_FORWARD);
   for (int it = 0; it < c.nt; ++it) {
     if (variant_ >= 2) {
       const bool snap = store_fields && it % c.snapshot_interval == 0;
@@ -1415,7 +1420,8 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
-  const bool use_graph = graph_wanted();
+  bool use_graph = graph_wanted();
+  const bool begun = use_graph;
   const LoopGraph *cached = nullptr;
   std::vector<unsigned long long> gkey;
   if (use_graph) {
@@ -1424,6 +1430,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
     gkey.push_back((unsigned long long)(uintptr_t)snapshots_[i_shot].as<char>());
     auto f = graphs_.find(gkey);
     if (f != graphs_.end()) cached = &f->second;
+    else if (graph_ < 0 && graph_seen_[gkey]++ == 0) use_graph = false;  // as in forward_simulate
   }
   if (cached) {
     PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
@@ -1449,7 +1456,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   AdjointInjectArgs aa{F(0), F(1), b_.data(), a_stf_ux_.as<>() + shot_rows,
                        a_stf_uz_.as<>() + shot_rows, rec_index_.as<int>(), rec_next_.as<int>(),
                        rec_heads_.as<int>(), n_rec_heads_, c.nt, 0, c.dt, c.dx * c.dz};
-  if (variant_ >= 2 && !use_graph) fused_begin(i_shot, POINT_ADJOINT);
+  if (variant_ >= 2 && !begun) fused_begin(i_shot, POINT_ADJOINT);
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
     // variant 5 retreats two steps per launch unless the second one correlates with a snapshot

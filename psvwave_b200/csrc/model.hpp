@@ -272,6 +272,7 @@ class Model {
   int graph_ = -1;  // -1 = auto (small grids only, see graph_wanted), 0 = off, 1 = on
   bool graph_wanted() const;
   std::map<std::vector<unsigned long long>, LoopGraph> graphs_;
+  std::map<std::vector<unsigned long long>, int> graph_seen_;  // auto mode: a loop is captured when it comes back
   std::vector<unsigned long long> graph_key(int direction, int i_shot, bool store) const;
   void graph_capture_begin();
   void graph_capture_abort();

@@ -105,3 +105,25 @@ def test_graph_replay_of_a_model_ensemble(tmp_path):
             for x, y in zip(a.get_synthetic_data(), b.get_synthetic_data()):
                 assert np.array_equal(x, y)
     assert ms[0]._get_option("graphs_cached") == 1
+
+
+def test_auto_mode_captures_a_loop_when_it_comes_back(tmp_path):
+    import psvwave_b200
+    ini = str(tmp_path / "g.ini")
+    config(ini)
+    plain, auto = psvwave_b200.fdModel(ini), psvwave_b200.fdModel(ini)
+    plain._set_option("graph", 0)
+    assert auto._get_option("graph") == -1
+    med = random_medium(auto.nx, auto.nz, seed=8)
+    plain.set_parameter_fields(*random_medium(auto.nx, auto.nz, seed=9))
+    for s in range(plain.n_shots):
+        plain.forward_simulate(s, False)
+    obs = plain.get_synthetic_data()
+    cached = []
+    for rnd in range(3):
+        run(plain, med, obs)
+        run(auto, med, obs)
+        cached.append(auto._get_option("graphs_cached"))
+        for a in ARRAYS:
+            assert np.array_equal(gpu_array(auto, a), gpu_array(plain, a)), f"round {rnd}: {a}"
+    assert cached == [0, 2 * auto.n_shots, 2 * auto.n_shots]
