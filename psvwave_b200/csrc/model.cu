@@ -895,9 +895,10 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
     const int n_strips = std::max(1, waves * pipe_resident_ / blocks_x);
     const int st = (nx + n_strips - 1) / n_strips;
     if (st <= 128 || n_strips >= nx) {
-      // small grids are bound by the serial latency of a CTA's march (~1 us per row), so short strips
-      // win although each recomputes 4 halo rows: 250x150, one model: 15.3 -> 10.2 us per step with 2 rows
-      *strip = std::max(st, 2);
+      // small grids are bound by the serial latency of a CTA's march (~0.6 us per row), so the shortest strips
+      // win although each re-reads 8 halo rows: 250x150, one model, under graph replay: 9.0 us per step with
+      // 6 rows, 5.9 with 2, 5.4 with 1 (profiles/r1o_graph_replay.md)
+      *strip = std::max(st, 1);
       return;
     }
   }

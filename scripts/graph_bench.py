@@ -61,5 +61,9 @@ def measure(options):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1:  # option sets as JSON objects on the command line
+        for a in sys.argv[1:]:
+            print(json.dumps(measure(json.loads(a))), flush=True)
+        sys.exit(0)
     for opts in ({"graph": 0}, {"graph": 0, "pdl": 1}, {"graph": 1}, {"graph": 1, "pdl": 1}, {}):
         print(json.dumps(measure(opts)), flush=True)
