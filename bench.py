@@ -21,8 +21,10 @@ from pinned host memory before, get_gradient_vector to the host after, inside th
 `roofline` is the dominant sweep kernel: algorithmic bytes per launch over its
 mean CUDA-event duration sampled inside the timed steps.
 `cpu_baseline` / `--impl reference`: the UNMODIFIED reference core (oracle/_ref, OpenMP, all
-host threads) on a bounded sample of the same workload (same grid and medium, fewer time
-steps).  Nothing here reads /root/reference at run time.
+host threads -- set explicitly, torchrun's OMP_NUM_THREADS=1 is overridden) on a bounded sample
+of the same workload: same grid and medium, NT_SAMPLE time steps (fixed, stated in both arms'
+`config`).  `parity` compares the CUDA path with that very reference run (seismograms, the
+three Lame kernels, the gradient) on the sample.  Nothing here reads /root/reference at run time.
 """
 from __future__ import annotations
 
@@ -42,6 +44,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 WORKLOAD = "C2-marmousi-scale-gradient"
+NT_SAMPLE = 400  # time steps of the reference arm / cpu_baseline sample (same grid, medium, sources, receivers)
 GEOM = dict(nx_inner=3000, nz_inner=1220, np_boundary=50, nt=4000, snapshot_interval=20, n_shots=16, nr=300)
 
 
@@ -157,31 +160,42 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # the reference arm / cpu baseline: unmodified reference core on a bounded sample
 # ---------------------------------------------------------------------------------------------
-def omp_threads() -> int:
+def host_threads() -> int:
+    """All the host threads this process may run on; also makes libgomp use them (torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which would silently time a one-thread reference)."""
     import ctypes
     try:
-        return int(ctypes.CDLL("libgomp.so.1").omp_get_max_threads())
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    n = max(1, n)
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        gomp = ctypes.CDLL("libgomp.so.1", mode=ctypes.RTLD_GLOBAL)
+        gomp.omp_set_dynamic(0)
+        gomp.omp_set_num_threads(n)
+        return int(gomp.omp_get_max_threads())
     except Exception:
-        return os.cpu_count() or 1
+        return n
 
 
-def cpu_sample_run(target_seconds: float, geom=GEOM, steps: int = 1, warmup: int = 0):
-    """Time forward(store)+adjoint of shot 0 on the CPU checker for `nt_sample` time steps of
-    the same grid/medium.  Returns (updates per second, seconds per step, description, kind)."""
+def cpu_sample_run(nt: int = NT_SAMPLE, geom=GEOM, steps: int = 1, warmup: int = 0, keep: bool = False):
+    """Time forward(store)+adjoint of shot 0 on the CPU checker for `nt` time steps of the same
+    grid/medium.  Returns a dict: rate (updates/s, best step), seconds per step (mean), sample text,
+    kind, nt, threads and -- with keep=True -- the arrays the parity check compares."""
+    threads = host_threads()
     from oracle import oracle
     kind = "reference" if oracle.ref_available() else "port"
-    si = geom["snapshot_interval"]
+    cfg = workload_config(nt, 1, geom)
+    d = tempfile.mkdtemp(prefix="psv_cpu_")
+    ini = os.path.join(d, "sample.ini")
+    write_ini(ini, cfg)
+    m = oracle.RefModel(ini) if kind == "reference" else oracle.OracleModel(ini)
+    m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
+    zero = np.zeros((1, m.nr, nt))  # observed data: explicitly zero (the reference leaves the arrays uninitialised)
+    m.set_observed_data(zero, zero)
 
-    def make(nt):
-        cfg = workload_config(nt, 1, geom)
-        d = tempfile.mkdtemp(prefix="psv_cpu_")
-        ini = os.path.join(d, "sample.ini")
-        write_ini(ini, cfg)
-        m = oracle.RefModel(ini) if kind == "reference" else oracle.OracleModel(ini)
-        m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
-        return m
-
-    def gradient(m):
+    def gradient():
         t0 = time.perf_counter()
         m.forward_simulate(0, True)
         m.calculate_l2_misfit()
@@ -191,39 +205,75 @@ def cpu_sample_run(target_seconds: float, geom=GEOM, steps: int = 1, warmup: int
         m.map_kernels_to_velocity()
         return time.perf_counter() - t0
 
-    m = make(si)  # calibration: one snapshot interval
-    gradient(m)
-    t_cal = gradient(m)
-    per_step = t_cal / si
-    nt = int(max(si, min(geom["nt"], 1000, round(target_seconds / per_step / si) * si)))
-    if nt != si:
-        del m
-        m = make(nt)
     for _ in range(warmup):
-        gradient(m)
-    times = [gradient(m) for _ in range(max(1, steps))]
+        gradient()
+    times = [gradient() for _ in range(max(1, steps))]
     updates = 2.0 * m.nx * m.nz * nt
     best = min(times)
-    sample = (f"{kind} core (OpenMP, -O3), shot 0 of {WORKLOAD}: same {m.nx}x{m.nz} grid and medium, "
-              f"nt={nt} of {geom['nt']} time steps, forward(store)+adjoint, best of {len(times)}")
-    return updates / best, sum(times) / len(times), sample, kind, nt
+    sample = (f"{kind} core (OpenMP, -O3, {threads} threads), shot 0 of {WORKLOAD}: same {m.nx}x{m.nz} grid and "
+              f"medium, nt={nt} of {geom['nt']} time steps, forward(store)+adjoint, best of {len(times)}")
+    out = dict(rate=updates / best, sec=sum(times) / len(times), sample=sample, kind=kind, nt=nt, threads=threads,
+               ini=ini)
+    if keep:
+        out["arrays"] = dict(ux=m.array("rtf_ux").copy(), uz=m.array("rtf_uz").copy(),
+                             kernels=np.stack([m.array(k).copy() for k in
+                                               ("lambda_kernel", "mu_kernel", "density_l_kernel")]),
+                             gradient=m.get_gradient_vector(), misfit=float(m.misfit))
+    return out
+
+
+def gpu_parity(ref: dict) -> dict:
+    """The CUDA path on the sample the reference just ran (same .ini, same medium, observed data zero):
+    relative L2 differences of what the hot path produces."""
+    import psvwave_b200
+    from psvwave_b200 import _array_ids  # noqa: F401  (name -> psv_array id)
+    m = psvwave_b200.fdModel(ref["ini"])
+    m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
+    zero = np.zeros((1, m.nr, m.nt))
+    m.set_observed_data(zero, zero)
+    m.forward_simulate(0, True)
+    m.calculate_l2_misfit()
+    m.calculate_l2_adjoint_sources()
+    m.reset_kernels()
+    m.adjoint_simulate(0)
+    m.map_kernels_to_velocity()
+    a = ref["arrays"]
+
+    def rel(x, y):
+        n = float(np.linalg.norm(y))
+        return float(np.linalg.norm(np.asarray(x) - y) / (n if n > 0 else 1.0))
+
+    ux, uz = m.get_synthetic_data()
+    ids = psvwave_b200._array_ids()
+    kern = np.stack([m._get_array(ids[k]).reshape(m.nx, m.nz) for k in
+                     ("lambda_kernel", "mu_kernel", "density_l_kernel")])
+    return {"against": ref["kind"], "nt": ref["nt"], "rel_l2_ux": rel(ux, a["ux"]), "rel_l2_uz": rel(uz, a["uz"]),
+            "rel_l2_kernels": rel(kern, a["kernels"]), "rel_l2_gradient": rel(m.get_gradient_vector(), a["gradient"]),
+            "rel_misfit": abs(m.misfit - a["misfit"]) / abs(a["misfit"]), "tolerance": 1e-10}
+
+
+def sample_config() -> dict:
+    return {"workload": WORKLOAD, "grid": [GEOM["nx_inner"] + 2 * GEOM["np_boundary"],
+                                           GEOM["nz_inner"] + 2 * GEOM["np_boundary"]],
+            "nt": GEOM["nt"], "snapshot_interval": GEOM["snapshot_interval"], "sources_per_shot": 2,
+            "receivers": GEOM["nr"], "reference_sample_nt": NT_SAMPLE}
 
 
 def run_reference_arm(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    threads = omp_threads()
-    rate, sec, sample, kind, nt = cpu_sample_run(12.0, steps=args.steps, warmup=min(args.warmup, 1))
+    r = cpu_sample_run(NT_SAMPLE, steps=args.steps, warmup=min(args.warmup, 1))
+    cfg = sample_config()
+    cfg["step"] = f"forward(store)+misfit+adjoint(+kernel accumulation) of one shot, {NT_SAMPLE} time steps per step"
     line = {
-        "impl": "reference", "metric": "grid-point updates/s (fwd+adj)", "value": rate, "unit": "updates/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "impl": "reference", "metric": "grid-point updates/s (fwd+adj)", "value": r["rate"], "unit": "updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["sec"] * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "grid": [GEOM["nx_inner"] + 2 * GEOM["np_boundary"],
-                                                  GEOM["nz_inner"] + 2 * GEOM["np_boundary"]],
-                   "nt_sample": nt, "nt": GEOM["nt"], "snapshot_interval": GEOM["snapshot_interval"]},
-        "cpu_baseline": {"value": rate, "unit": "updates/s", "cores": threads, "kind": kind, "sample": sample},
-        "e2e": {"value": rate, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": cfg,
+        "cpu_baseline": {"value": r["rate"], "unit": "updates/s", "cores": r["threads"], "kind": r["kind"],
+                         "sample": r["sample"]},
+        "e2e": {"value": r["rate"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
@@ -310,7 +360,7 @@ def run_ours(args) -> None:
             dist.barrier()
             torch.cuda.synchronize()
 
-    m._set_option("profile", 1)
+    m._set_option("profile", 1)  # CUDA events around ~32 sampled plain launches per time loop (< 0.1 % of a step)
     for i in range(args.warmup):
         step(my[i], False)
     barrier()
@@ -326,6 +376,11 @@ def run_ours(args) -> None:
         barrier()
         wall_ms = (time.perf_counter() - t_wall) * 1e3
     m._set_option("profile", 0)
+    # one more step without the sampling events: what the default configuration does (reported, not the headline)
+    barrier()
+    m._timer_start()
+    step(my[args.warmup], False)
+    unprofiled_ms = m._timer_stop()
 
     # end to end through the public API with host buffers
     barrier()
@@ -357,49 +412,63 @@ def run_ours(args) -> None:
         P = np.array(profs)  # columns: fwd stress, fwd velocity, adj stress, adj velocity (ms / launch)
         pts = float(nx) * nz
         bytes_per_launch = {"stress": 12 * 8 * pts, "velocity": 10 * 8 * pts, "fused": 16 * 8 * pts}
+        moved_per_launch = {"stress": 10 * 8 * pts, "velocity": 8 * 8 * pts, "fused": 13 * 8 * pts}
         fused = m._get_option("variant") >= 2
         fp32 = bool(m._get_option("fp32"))  # optional mode, never the default: words are 4 bytes there
         if fp32:
             bytes_per_launch = {k: v / 2 for k, v in bytes_per_launch.items()}
+            moved_per_launch = {k: v / 2 for k, v in moved_per_launch.items()}
         if fused:
             ms = float(P[:, [0, 2]].mean())
-            kern, nbytes = "fused stress+velocity sweep", bytes_per_launch["fused"]
-            if m._get_option("variant") == 5 and not fp32:
-                # the sampled launches of variant 5 are its two-step launches: 2 grid-point updates
-                # per point, each credited with the single-pass 128 B (SURVEY §8d)
+            kern, nbytes, moved = "fused stress+velocity sweep", bytes_per_launch["fused"], moved_per_launch["fused"]
+            if m._get_option("variant") == 4 and not fp32:
+                # the sampled launches of variant 4 are its two-step launches: 2 grid-point updates
+                # per point, each credited with the single-pass 128 B (SURVEY 8d)
                 kern, nbytes = "fused two-step sweep", 2 * bytes_per_launch["fused"]
         else:
             s_ms, v_ms = float(P[:, [0, 2]].mean()), float(P[:, [1, 3]].mean())
             if s_ms >= v_ms:
-                kern, ms, nbytes = "stress sweep", s_ms, bytes_per_launch["stress"]
+                kern, ms, nbytes, moved = "stress sweep", s_ms, bytes_per_launch["stress"], moved_per_launch["stress"]
             else:
-                kern, ms, nbytes = "velocity sweep", v_ms, bytes_per_launch["velocity"]
+                kern, ms, nbytes, moved = ("velocity sweep", v_ms, bytes_per_launch["velocity"],
+                                           moved_per_launch["velocity"])
         achieved = nbytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
-        traffic = None
+        traffic, traffic_source = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath) and not fp32:  # the capture is of the default FP64 step kernel
-            traffic = json.load(open(tpath)).get(kern)
+        if os.path.exists(tpath) and not fp32:  # an ncu capture of the default FP64 step kernel, not of this run
+            tj = json.load(open(tpath))
+            traffic, traffic_source = tj.get(kern), "profiles/traffic.json (" + str(tj.get("_source", "ncu --set full")) + ")"
+        real = traffic if traffic else moved
         roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": nbytes, "ms_per_launch": ms,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_source,
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": nbytes, "ms_per_launch": ms,
+                    "note": "achieved/frac credit the single-pass ALGORITHMIC 128 B per update (SURVEY 8d); the kernel "
+                            "moves fewer bytes (la, b_vz, taper are not streamed): moved_* is the bandwidth on the bus",
+                    "moved_bytes_per_launch": real, "moved_gbs": real / (ms * 1e-3) / 1e9 if ms > 0 else 0.0,
+                    "moved_frac": (real / (ms * 1e-3) / 1e9) / peak if ms > 0 else 0.0,
                     "all_ms_per_launch": {"fwd_stress": float(P[:, 0].mean()), "fwd_velocity": float(P[:, 1].mean()),
                                           "adj_stress": float(P[:, 2].mean()), "adj_velocity": float(P[:, 3].mean())}}
-        cpu = None
+        cpu = parity = None
         if world == 1 and not args.no_cpu_baseline:
-            rate, _, sample, kind, _ = cpu_sample_run(15.0)
-            cpu = {"value": rate, "unit": "updates/s", "cores": omp_threads(), "kind": kind, "sample": sample}
+            r = cpu_sample_run(NT_SAMPLE, keep=True)
+            cpu = {"value": r["rate"], "unit": "updates/s", "cores": r["threads"], "kind": r["kind"],
+                   "sample": r["sample"]}
+            parity = gpu_parity(r)
+        cfg_out = sample_config()
+        cfg_out.update({"grid": [nx, nz], "nt": nt, "snapshot_interval": m.snapshot_interval,
+                        "shots_per_gpu_per_step": 1, "receivers": m.nr,
+                        "step": "forward(store)+misfit+adjoint(+kernel accumulation)" + ("+allreduce" if world > 1 else ""),
+                        "parallelism": f"shots x{world}", "variant": m._get_option("variant"),
+                        "exact": m._get_option("exact"),
+                        "l2": f"working set {(8 * nx * nz * 8) >> 20} MiB per sweep > 126 MB L2 (no flush needed)"})
         line = {
             "metric": "grid-point updates/s (fwd+adj)", "value": value, "unit": "updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 wavefield, f64 seismograms/kernels (optional mode)" if fp32 else "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "grid": [nx, nz], "nt": nt, "snapshot_interval": m.snapshot_interval,
-                       "shots_per_gpu_per_step": 1, "sources_per_shot": 2, "receivers": m.nr,
-                       "step": "forward(store)+misfit+adjoint(+kernel accumulation)" + ("+allreduce" if world > 1 else ""),
-                       "parallelism": f"shots x{world}", "variant": m._get_option("variant"),
-                       "exact": m._get_option("exact"),
-                       "l2": f"working set {(8 * nx * nz * 8) >> 20} MiB per sweep > 126 MB L2 (no flush needed)"},
+            "config": cfg_out,
             "gradient_ms_per_shot": dev_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "unprofiled_ms_per_step": unprofiled_ms,
             "clocks": clocks.summary(),
             "e2e": {"value": e2e_value, "unit": "updates/s", "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": int(sum(a.nbytes for a in host_model)), "d2h_bytes_per_step": grad_bytes},
@@ -408,6 +477,7 @@ def run_ours(args) -> None:
         }
         if cpu:
             line["cpu_baseline"] = cpu
+            line["parity"] = parity
         emit(line)
     if world > 1:
         dist.barrier()

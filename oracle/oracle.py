@@ -213,6 +213,36 @@ class _OrcConfig(C.Structure):
     ]
 
 
+class FullConfig(C.Structure):
+    """include/psvwave_b200.h `psv_config` = oracle/ref_shim.cpp `ref_config`: the reference's explicit
+    30-argument constructor (src/fdModel.h:50-64) as one flat record."""
+    _fields_ = _OrcConfig._fields_ + [("observed_data_folder", C.c_char_p), ("stf_folder", C.c_char_p)]
+
+
+def full_config(cfg: dict):
+    """(FullConfig, keep-alive list) from a config dict as returned by config_from_ini."""
+    which = cfg["which_source_to_fire_in_which_shot"]
+    offs = np.zeros(cfg["n_shots"] + 1, dtype=np.int32)
+    offs[1:] = np.cumsum([len(s) for s in which])
+    keep = [np.array(cfg["ix_sources"], dtype=np.int32), np.array(cfg["iz_sources"], dtype=np.int32),
+            np.array(cfg["moment_angles"], dtype=np.float64), offs,
+            np.array([s for sub in which for s in sub], dtype=np.int32),
+            np.array(cfg["ix_receivers"], dtype=np.int32), np.array(cfg["iz_receivers"], dtype=np.int32)]
+    ip = lambda a: a.ctypes.data_as(C.POINTER(C.c_int))  # noqa: E731
+    c = FullConfig()
+    for k in ("nt", "nx_inner", "nz_inner", "nx_inner_boundary", "nz_inner_boundary", "dx", "dz", "dt", "np_boundary",
+              "np_factor", "scalar_rho", "scalar_vp", "scalar_vs", "npx", "npz", "peak_frequency", "source_timeshift",
+              "delay_cycles_per_shot", "n_sources", "n_shots", "nr", "snapshot_interval"):
+        setattr(c, k, cfg[k])
+    c.ix_sources, c.iz_sources = ip(keep[0]), ip(keep[1])
+    c.moment_angles = keep[2].ctypes.data_as(C.POINTER(C.c_double))
+    c.shot_offsets, c.shot_sources = ip(keep[3]), ip(keep[4])
+    c.ix_receivers, c.iz_receivers = ip(keep[5]), ip(keep[6])
+    c.observed_data_folder = str(cfg.get("observed_data_folder", ".")).encode()
+    c.stf_folder = str(cfg.get("stf_folder", ".")).encode()
+    return c, keep
+
+
 def _load(path: str, prefix: str):
     lib = C.CDLL(path)
     f = lambda n: getattr(lib, prefix + n)  # noqa: E731
@@ -471,11 +501,20 @@ class RefModel(_CpuModel):
         lib.ref_adjoint.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.ref_run_model.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.ref_load_receivers.argtypes = [C.c_void_p, C.c_int]
+        lib.ref_write_kernels.argtypes = [C.c_void_p]
+        lib.ref_load_model.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+        lib.ref_forward_dump.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        lib.ref_create_explicit.restype = C.c_void_p
+        lib.ref_create_explicit.argtypes = [C.POINTER(FullConfig)]
         for n in ("update_from_velocity", "calculate_l2_misfit", "calculate_l2_adjoint_sources",
                   "reset_kernels", "map_kernels_to_velocity", "write_receivers", "write_sources"):
             getattr(lib, "ref_" + n).argtypes = [C.c_void_p]
         self._lib = lib
-        self._h = lib.ref_create(ini_path.encode())
+        if isinstance(ini_path, dict):  # the explicit constructor (src/fdModel.h:50-64)
+            c, keep = full_config(ini_path)
+            self._h = lib.ref_create_explicit(C.byref(c))
+        else:
+            self._h = lib.ref_create(ini_path.encode())
         if not self._h:
             raise ValueError(lib.ref_last_error().decode())
 
@@ -491,7 +530,10 @@ class RefModel(_CpuModel):
 
     def forward_simulate(self, i_shot, store_fields=True, verbose=False, output_wavefields=False,
                          omp_threads_override=0):
-        self._chk(self._lib.ref_forward(self._h, i_shot, int(store_fields), int(verbose)))
+        if output_wavefields:
+            self._chk(self._lib.ref_forward_dump(self._h, i_shot, int(store_fields), 1))
+        else:
+            self._chk(self._lib.ref_forward(self._h, i_shot, int(store_fields), int(verbose)))
 
     def adjoint_simulate(self, i_shot, verbose=False, omp_threads_override=0):
         self._chk(self._lib.ref_adjoint(self._h, i_shot, int(verbose)))
@@ -522,3 +564,9 @@ class RefModel(_CpuModel):
 
     def write_sources(self):
         self._chk(self._lib.ref_write_sources(self._h))
+
+    def write_kernels(self):
+        self._chk(self._lib.ref_write_kernels(self._h))
+
+    def load_model(self, de_path, vp_path, vs_path, verbose=False):
+        self._chk(self._lib.ref_load_model(self._h, de_path.encode(), vp_path.encode(), vs_path.encode(), int(verbose)))

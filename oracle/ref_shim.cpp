@@ -13,6 +13,7 @@
 #include <cstring>
 #include <exception>
 #include <string>
+#include <vector>
 
 #include "fdModel.h"
 
@@ -182,6 +183,59 @@ int ref_load_receivers(void *h, int verbose) {
 }
 int ref_write_sources(void *h) {
   return guarded([&] { static_cast<fdModel *>(h)->write_sources(); });
+}
+// files in the current directory: kernel_vp.txt kernel_vs.txt kernel_density.txt (src/fdModel.cpp:1326-1356)
+int ref_write_kernels(void *h) {
+  return guarded([&] { static_cast<fdModel *>(h)->write_kernels(); });
+}
+int ref_load_model(void *h, const char *de_path, const char *vp_path, const char *vs_path, int verbose) {
+  return guarded([&] { static_cast<fdModel *>(h)->load_model(de_path, vp_path, vs_path, verbose != 0); });
+}
+// forward run with the wavefield dumps into ./snapshots/ (src/fdModel.cpp:753-776)
+int ref_forward_dump(void *h, int i_shot, int store_fields, int output_wavefields) {
+  return guarded([&] {
+    static_cast<fdModel *>(h)->forward_simulate(i_shot, store_fields != 0, false, output_wavefields != 0);
+  });
+}
+
+// The explicit 30-argument constructor (src/fdModel.h:50-64), fed from the same flat record the
+// C ABI's psv_create takes (include/psvwave_b200.h: psv_config).
+struct ref_config {
+  int nt, nx_inner, nz_inner, nx_inner_boundary, nz_inner_boundary;
+  double dx, dz, dt;
+  int np_boundary;
+  double np_factor;
+  double scalar_rho, scalar_vp, scalar_vs;
+  int npx, npz;
+  double peak_frequency, source_timeshift, delay_cycles_per_shot;
+  int n_sources, n_shots;
+  const int *ix_sources, *iz_sources;
+  const double *moment_angles;
+  const int *shot_offsets;
+  const int *shot_sources;
+  int nr;
+  const int *ix_receivers, *iz_receivers;
+  int snapshot_interval;
+  const char *observed_data_folder, *stf_folder;
+};
+
+void *ref_create_explicit(const ref_config *c) {
+  fdModel *m = nullptr;
+  const int rc = guarded([&] {
+    std::vector<std::vector<int>> which;
+    for (int s = 0; s < c->n_shots; ++s)
+      which.emplace_back(c->shot_sources + c->shot_offsets[s], c->shot_sources + c->shot_offsets[s + 1]);
+    m = new fdModel(c->nt, c->nx_inner, c->nz_inner, c->nx_inner_boundary, c->nz_inner_boundary, c->dx, c->dz, c->dt,
+                    c->np_boundary, c->np_factor, c->scalar_rho, c->scalar_vp, c->scalar_vs, c->npx, c->npz,
+                    c->peak_frequency, c->source_timeshift, c->delay_cycles_per_shot, c->n_sources, c->n_shots,
+                    std::vector<int>(c->ix_sources, c->ix_sources + c->n_sources),
+                    std::vector<int>(c->iz_sources, c->iz_sources + c->n_sources),
+                    std::vector<double>(c->moment_angles, c->moment_angles + c->n_sources), which, c->nr,
+                    std::vector<int>(c->ix_receivers, c->ix_receivers + c->nr),
+                    std::vector<int>(c->iz_receivers, c->iz_receivers + c->nr), c->snapshot_interval,
+                    c->observed_data_folder, c->stf_folder);
+  });
+  return rc == 0 ? m : nullptr;
 }
 
 } // extern "C"

@@ -32,66 +32,9 @@
 
 #include <cstdio>
 
-#include "kernels.cuh"
-#include "pointwise.cuh"
+#include "fused_types.cuh"
 
 namespace psv {
-
-constexpr int kFusedOwnedPairs = 28;  // lanes 2..29 of a warp
-
-// Injection operation bucketed by row (sorted by target row, original order kept).
-struct RowOp {
-  int z;          // target column
-  int field;      // 0 = vx, 1 = vz
-  int source;     // row of stf
-  int x;          // target row (local)
-  double weight;  // moment entry (x0.25 where the reference does)
-  double sign;    // +1 / -1
-  double d4;      // dx^4 or dz^4
-  double rd4;     // 1 / d4 (default arithmetic multiplies, "exact" divides like the reference)
-};
-
-enum PointMode { POINT_NONE = 0, POINT_FORWARD = 1, POINT_ADJOINT = 2 };
-
-struct FusedModel {  // per-model pointers (constant during one simulate call)
-  double *f[2][5];   // ping-pong state: [parity][vx vz txx tzz txz]
-  const double *lm, *mu, *b;
-  double *snap;      // this shot's snapshots [5][n_snap_alloc][nx*ld]
-  double *k_lam, *k_mu, *k_rho;
-  double *ux, *uz;        // synthetics of this shot [nr][nt]      (POINT_FORWARD)
-  const double *ax, *az;  // adjoint sources of this shot [nr][nt] (POINT_ADJOINT)
-};
-
-struct FusedCommon {
-  GridShape g;
-  SweepConsts k;
-  const double *taper_table;
-  int parity;       // old state = f[parity], new state = f[parity ^ 1]
-  int n_zwarps;     // ceil(ld/2 / 28)
-  int strip;        // rows per warp
-  int tile_pairs;   // variant 5: z-pairs per CTA tile
-  int pdl;             // variant 3: launched with programmatic stream serialization (see fused_pipe_kernel)
-  int rec_increments;  // 1: receiver samples are stored as increments, the running sum follows the time loop
-  int l2_mode;      // variant 3: bit 0 = medium rows evict_last in L2, bit 1 = state rows evict_first
-  int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
-  size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
-  // snapshots / kernel accumulation
-  size_t snap_field_stride;  // n_snap_alloc * nx*ld
-  size_t snap_offset;        // snapshot index * nx*ld
-  int wx0, wx1, wz0, wz1;
-  double sidt;
-  // point operations
-  int point_mode;
-  int nt, it;
-  double dt, dxdz, rdxdz;  // rdxdz = 1 / (dx*dz), default arithmetic only
-  const int *rec_row_start;  // [nx+1] CSR over rows of the receivers sorted by (ix, r)
-  const int *rec_z;          // column of sorted receiver q
-  const int *rec_x;          // row of sorted receiver q
-  const int *rec_id;         // original receiver number of sorted receiver q
-  const int *op_row_start;   // [nx+1] CSR over rows of this shot's injection operations
-  const RowOp *ops;
-  const double *stf;         // [n_sources][nt]
-};
 
 __device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 __device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
@@ -727,123 +670,6 @@ __global__ void __launch_bounds__((NW + 1) * 32) fused_pipe_kernel(const FusedCo
   GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
                   m.f[c.parity ^ 1][4], xs, xe, own};
   fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xs, xe, xs, xe, own, own, c.it});
-}
-
-// ------------------------------------------------------------------------------------------
-// Variant 6: variant 3 without a producer warp.  The step kernel is bound by issue latency (two
-// resident warps per scheduler at ~160 registers), not by HBM, so the thirteenth warp of a CTA is
-// better spent marching: 12 consumer warps = 384 threads keep the 168-register budget (416 threads
-// would be capped at 128 and spill).  The bulk copies of row j are issued by lane 0 of warp
-// (j - j0) mod NW, `la` rows ahead of its own march, so the producer work is spread evenly and no
-// warp paces the others.  Ring, barriers, slot contents and arithmetic are those of variant 3.
-// ------------------------------------------------------------------------------------------
-template <int MODE, int NW>
-struct CoopRows {
-  PipeRows ring;
-  const FusedCommon *c;
-  const FusedModel *m;
-  int warp, j0, last, la;  // first / last row of the march, rows of lookahead
-  int kp_tile, cx0, cx1;   // first pair of a row segment; correlation rows of this strip
-  unsigned ring_u32;
-  __device__ __forceinline__ void issue(int j) {
-    using G = PipeGeom<NW>;
-    const int n = j - j0, slot = n % ring.stages;
-    mbar_wait(ring.empty0 + 8 * slot, (((unsigned)(n / ring.stages)) & 1u) ^ 1u);
-    const unsigned bar = ring.full0 + 8 * slot;
-    const bool corr = MODE == MODE_ACCUMULATE && j >= cx0 && j < cx1;
-    mbar_expect_tx(bar, corr ? G::kSeg * kPipeArraysCorr : G::kStage);
-    const unsigned dst = ring_u32 + slot * ring.stage_bytes;
-    const long long ld2n = ring.ld2n;
-    const long long off = (long long)j * ld2n + kp_tile;
-    const double2 *f0 = reinterpret_cast<const double2 *>(m->f[c->parity][0]) + off;
-    const long long fs2 = (long long)(c->field_stride >> 1);
-    bulk_g2s(dst, f0 + 2 * ld2n, G::kSeg, bar);
-    bulk_g2s(dst + G::kSeg, f0 + fs2 + ld2n, G::kSeg, bar);
-    bulk_g2s(dst + 2 * G::kSeg, f0 + 2 * fs2, G::kSeg, bar);
-    bulk_g2s(dst + 3 * G::kSeg, f0 + 3 * fs2, G::kSeg, bar);
-    bulk_g2s(dst + 4 * G::kSeg, f0 + 4 * fs2, G::kSeg, bar);
-    bulk_g2s(dst + 5 * G::kSeg, reinterpret_cast<const double2 *>(m->lm) + off, G::kSeg, bar);
-    bulk_g2s(dst + 6 * G::kSeg, reinterpret_cast<const double2 *>(m->mu) + off, G::kSeg, bar);
-    bulk_g2s(dst + 7 * G::kSeg, reinterpret_cast<const double2 *>(m->b) + off - 2 * ld2n, G::kSeg, bar);
-    if (corr) {
-      const double *snap0 = m->snap + c->snap_offset;
-#pragma unroll
-      for (int f = 0; f < 5; ++f)
-        bulk_g2s(dst + (8 + f) * G::kSeg, reinterpret_cast<const double2 *>(snap0 + f * c->snap_field_stride) + off,
-                 G::kSeg, bar);
-      bulk_g2s(dst + 13 * G::kSeg, reinterpret_cast<const double2 *>(m->k_rho) + off, G::kSeg, bar);
-      bulk_g2s(dst + 14 * G::kSeg, reinterpret_cast<const double2 *>(m->k_lam) + off, G::kSeg, bar);
-      bulk_g2s(dst + 15 * G::kSeg, reinterpret_cast<const double2 *>(m->k_mu) + off, G::kSeg, bar);
-    }
-  }
-  __device__ __forceinline__ void maybe_issue(int j) {
-    if (j <= last && (j - j0) % NW == warp && ring.lane == 0) issue(j);
-  }
-  __device__ __forceinline__ void prologue(int j, long long r, MarchWindow &w) {
-    for (int jj = j; jj < j + la; ++jj) maybe_issue(jj);
-    __syncwarp();
-    ring.prologue(j, r, w);
-  }
-  __device__ __forceinline__ void fetch(int j, long long r, RowData &d) {
-    maybe_issue(j + la);
-    __syncwarp();
-    ring.fetch(j, r, d);
-  }
-  __device__ __forceinline__ void fetch_corr(const FusedCommon &cc, const FusedModel &mm, long long r, bool lane_ok,
-                                             CorrData &q) const {
-    ring.fetch_corr(cc, mm, r, lane_ok, q);
-  }
-  __device__ __forceinline__ void release() { ring.release(); }
-};
-
-template <class M, int MODE, int NW>
-__global__ void __launch_bounds__(NW * 32) fused_coop_kernel(const FusedCommon c, const FusedModel *__restrict__ models,
-                                                             const int stages) {
-  using G = PipeGeom<NW>;
-  extern __shared__ __align__(128) unsigned char psv_smem[];
-  unsigned long long *bars = reinterpret_cast<unsigned long long *>(psv_smem);
-  unsigned char *ring = psv_smem + 128 * ((2 * stages * 8 + 127) / 128);
-  const unsigned full0 = smem_u32(bars), empty0 = full0 + 8 * stages;
-  constexpr int kSlotBytes = G::kSeg * (MODE == MODE_ACCUMULATE ? kPipeArraysCorr : kPipeArrays);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < stages; ++s) {
-      mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, NW);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-
-  const FusedModel &m = models[blockIdx.z];
-  const long long ld2n = c.g.ld >> 1;
-  const int xs = blockIdx.y * c.strip;
-  const int xe = min(xs + c.strip, c.g.nx);
-  const int kp_tile = blockIdx.x * G::kOwned - 2;
-  PipeRows pr{ring, full0, empty0, stages, G::kSeg, kSlotBytes, (warp * kFusedOwnedPairs + lane) * 16, 0, 0u, lane,
-              m.f[c.parity][0], m.f[c.parity][1], ld2n, MODE == MODE_ACCUMULATE};
-  CoopRows<MODE, NW> rows{pr, &c, &m, warp, xs - 2, xe + 1, max(stages - 2, 1), kp_tile, max(xs, c.wx0), min(xe, c.wx1),
-                          smem_u32(ring)};
-  const int kp = kp_tile + warp * kFusedOwnedPairs + lane;
-  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
-  GlobalSink sink{m.f[c.parity ^ 1][0], m.f[c.parity ^ 1][1], m.f[c.parity ^ 1][2], m.f[c.parity ^ 1][3],
-                  m.f[c.parity ^ 1][4], xs, xe, own};
-  fused_march<M, MODE>(c, m, rows, sink, lane, kp, MarchRange{xs, xe, xs, xe, own, own, c.it});
-}
-
-// Running sum of the receiver increments the marches stored (src/fdModel.cpp:584-594): u[it] = u[it-1] + s[it],
-// one thread per trace and model (blockIdx.y), the reference's sequential order and rounding.
-__global__ void receiver_prefix_models_kernel(const FusedModel *__restrict__ models, int nr, int nt) {
-  const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= 2 * nr) return;
-  const FusedModel &m = models[blockIdx.y];
-  double *u = (r < nr ? m.ux : m.uz) + (size_t)(r % nr) * nt;
-  double acc = u[0];
-  for (int it = 1; it < nt; ++it) {
-    acc = __dadd_rn(acc, u[it]);
-    u[it] = acc;
-  }
 }
 
 }  // namespace psv

@@ -17,15 +17,6 @@
 
 namespace psv {
 
-struct FusedModel32 {  // per-model pointers of the FP32 mode
-  float *f[2][5];      // ping-pong state: [parity][vx vz txx tzz txz]
-  const float *lm, *mu, *b;
-  float *snap;         // this shot's snapshots [5][n_snap_alloc][nx*ld], single precision
-  double *k_lam, *k_mu, *k_rho;
-  double *ux, *uz;
-  const double *ax, *az;
-};
-
 struct Consts32 {
   float sdt, rdx, rdz, c1, c2;
 };
@@ -277,16 +268,6 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
     xz_m3 = xz_m2; xz_m2 = xz_m1; xz_m1 = txz;
     zz_m2 = zz_m1; zz_m1 = tzz;
   }
-}
-
-// double <-> float images of grid arrays (medium refresh, getters)
-__global__ void to_float_kernel(const double *__restrict__ in, float *__restrict__ out, size_t n) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = (float)in[i];
-}
-__global__ void to_double_kernel(const float *__restrict__ in, double *__restrict__ out, size_t n) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = (double)in[i];
 }
 
 }  // namespace psv

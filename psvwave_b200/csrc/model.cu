@@ -12,12 +12,9 @@
 #include <type_traits>
 #include <sstream>
 
-#include "fused.cuh"
-#include "fused32.cuh"
 #include "kernels.cuh"
+#include "launchers.hpp"
 #include "pointwise.cuh"
-#include "pair.cuh"
-#include "window.cuh"
 
 namespace psv {
 
@@ -351,12 +348,14 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   fused_strip_ = o.fused_strip_;
   fused_block_ = o.fused_block_;
   pipe_stages_ = o.pipe_stages_;
-  win_config_ = o.win_config_;
   pipe_warps_ = o.pipe_warps_;
   l2_mode_ = o.l2_mode_;
   pdl_ = o.pdl_;
   graph_ = o.graph_;
-  coop_stages_ = o.coop_stages_;
+  pair_warps_ = o.pair_warps_;
+  pair_stages_ = o.pair_stages_;
+  pair_strip_ = o.pair_strip_;
+  l2_persist_mb_ = o.l2_persist_mb_;
   fp32_ = o.fp32_;
   PSV_CUDA(cudaStreamSynchronize(o.stream_));
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
@@ -684,23 +683,12 @@ const double *Model::field_as_double(int k) {
   return conv_.data();
 }
 
-namespace {
-template <class M>
-void launch_fused_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int block,
-                    cudaStream_t st) {
-  if (mode == MODE_SNAPSHOT) fused_step_kernel<M, MODE_SNAPSHOT><<<grid, block, 0, st>>>(fc, models);
-  else if (mode == MODE_ACCUMULATE) fused_step_kernel<M, MODE_ACCUMULATE><<<grid, block, 0, st>>>(fc, models);
-  else fused_step_kernel<M, MODE_PLAIN><<<grid, block, 0, st>>>(fc, models);
-}
-}  // namespace
-
 // Rows per warp such that the launch is a whole number of waves of resident blocks (the warps
 // of a launch run in lock-step through their strips, so a partial last wave costs a full one).
 int Model::fused_auto_strip(int n_zwarps, int batch) {
   if (fused_resident_blocks_ == 0) {
     int per_sm = 0, sms = 0;
-    PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_step_kernel<FastMath, MODE_PLAIN>,
-                                                           fused_block_, 0));
+    per_sm = fused_step_occupancy(fused_block_);
     PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
     fused_resident_blocks_ = std::max(1, per_sm * sms);
   }
@@ -713,146 +701,6 @@ int Model::fused_auto_strip(int n_zwarps, int batch) {
     if (strip <= 96 || n_strips >= nx) return std::max(strip, 8);
   }
 }
-
-namespace {
-template <class M, int MODE, int NW>
-void launch_pipe_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
-                   cudaStream_t st) {
-  static size_t configured = 0;  // per instantiation
-  if (configured < smem) {
-    PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<M, MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    configured = smem;
-  }
-  if (fc.pdl) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid;
-    cfg.blockDim = dim3((NW + 1) * 32);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    PSV_CUDA(cudaLaunchKernelEx(&cfg, fused_pipe_kernel<M, MODE, NW>, fc, models, stages));
-    return;
-  }
-  fused_pipe_kernel<M, MODE, NW><<<grid, (NW + 1) * 32, smem, st>>>(fc, models, stages);
-}
-template <class M, int NW>
-void launch_pipe_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
-                   cudaStream_t st) {
-  if (mode == MODE_SNAPSHOT) launch_pipe_k<M, MODE_SNAPSHOT, NW>(fc, models, grid, stages, smem, st);
-  else if (mode == MODE_ACCUMULATE) launch_pipe_k<M, MODE_ACCUMULATE, NW>(fc, models, grid, stages, smem, st);
-  else launch_pipe_k<M, MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
-}
-template <int NW>
-size_t pipe_smem_bytes(int stages, int arrays = kPipeArrays) {
-  return 128 * ((2 * (size_t)stages * 8 + 127) / 128) + (size_t)stages * PipeGeom<NW>::kSeg * arrays;
-}
-constexpr size_t kMaxPipeSmem = 232448;  // 227 KB per CTA on sm_100
-// correlation launches stage 16 segments per row: as many ring slots as fit, at most `stages`
-template <int NW>
-int pipe_corr_stages(int stages) {
-  while (stages > 2 && pipe_smem_bytes<NW>(stages, kPipeArraysCorr) > kMaxPipeSmem) --stages;
-  return stages;
-}
-}  // namespace
-
-// ---- variant 4: shared-memory window (window.cuh) ----------------------------------------------
-namespace {
-struct WinConfig {  // compiled (consumer warps, ring-T depth, min CTAs/SM) triples
-  int nw, st, minb;
-};
-constexpr WinConfig kWinConfigs[] = {{4, 2, 3}, {10, 2, 1}, {8, 2, 1}, {10, 4, 1}, {4, 4, 2}, {12, 2, 1}};
-constexpr int kWinConfigCount = sizeof(kWinConfigs) / sizeof(kWinConfigs[0]);
-
-template <class M, int MODE, int NW, int ST, int MINB>
-void launch_win_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream, int *occupancy) {
-  static bool configured = false;  // per instantiation
-  auto kern = window_step_kernel<M, MODE, NW, ST, MINB>;
-  constexpr int smem = WinLayout<NW, ST>::kTotal;
-  if (!configured) {
-    PSV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
-  if (occupancy) {
-    PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occupancy, kern, (NW + 1) * 32, smem));
-    return;
-  }
-  kern<<<grid, (NW + 1) * 32, smem, stream>>>(fc, models);
-}
-template <class M, int NW, int ST, int MINB>
-void launch_win_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream, int *occ) {
-  if (mode == MODE_SNAPSHOT) launch_win_k<M, MODE_SNAPSHOT, NW, ST, MINB>(fc, models, grid, stream, occ);
-  else if (mode == MODE_ACCUMULATE) launch_win_k<M, MODE_ACCUMULATE, NW, ST, MINB>(fc, models, grid, stream, occ);
-  else launch_win_k<M, MODE_PLAIN, NW, ST, MINB>(fc, models, grid, stream, occ);
-}
-template <class M>
-void launch_win(int cfg, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, cudaStream_t stream,
-                int *occ) {
-  switch (cfg) {
-    case 0: return launch_win_m<M, 4, 2, 3>(mode, fc, models, grid, stream, occ);
-    case 1: return launch_win_m<M, 10, 2, 1>(mode, fc, models, grid, stream, occ);
-    case 2: return launch_win_m<M, 8, 2, 1>(mode, fc, models, grid, stream, occ);
-    case 3: return launch_win_m<M, 10, 4, 1>(mode, fc, models, grid, stream, occ);
-    case 4: return launch_win_m<M, 4, 4, 2>(mode, fc, models, grid, stream, occ);
-    default: return launch_win_m<M, 12, 2, 1>(mode, fc, models, grid, stream, occ);
-  }
-}
-}  // namespace
-
-void Model::win_geometry(int batch, int *tiles, int *strip) {
-  const int nw = kWinConfigs[win_config_].nw;
-  const int owned = nw * kWinOwned;
-  *tiles = (ld_ / 2 + owned - 1) / owned;
-  if (win_resident_ == 0) {
-    int per_sm = 0, sms = 0;
-    FusedCommon dummy{};
-    launch_win<FastMath>(win_config_, MODE_PLAIN, dummy, nullptr, dim3(1), stream_, &per_sm);
-    PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
-    win_resident_ = std::max(1, per_sm * sms);
-  }
-  if (fused_strip_ > 0) {
-    *strip = fused_strip_;
-    return;
-  }
-  const int blocks_x = *tiles * batch;
-  const int nx = cfg_.nx;
-  for (int waves = 1;; ++waves) {
-    const int n_strips = std::max(1, waves * win_resident_ / blocks_x);
-    const int s = (nx + n_strips - 1) / n_strips;
-    if (s <= 128 || n_strips >= nx) {
-      *strip = std::max(s, 8);
-      return;
-    }
-  }
-}
-
-// Launch geometry of variant 3: CTAs per row, and rows per CTA such that the launch is a whole
-// number of waves of resident CTAs.
-namespace {
-// compiled consumer-warp counts of variant 3
-template <class F>
-auto with_pipe_warps(int nw, F &&f) {
-  switch (nw) {
-    case 12: return f(std::integral_constant<int, 12>{});
-    case 8: return f(std::integral_constant<int, 8>{});
-    case 4: return f(std::integral_constant<int, 4>{});
-    default: return f(std::integral_constant<int, 3>{});
-  }
-}
-template <int NW>
-int pipe_occupancy(size_t smem) {
-  int per_sm = 0;
-  PSV_CUDA(cudaFuncSetAttribute(fused_pipe_kernel<FastMath, MODE_PLAIN, NW>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, NW>,
-                                                         (NW + 1) * 32, smem));
-  return per_sm;
-}
-}  // namespace
 
 // Consumer warps per CTA of variant 3: the compiled width (8, 4 or 3 warps of 28 pairs) that covers
 // a row with the fewest warps; wide rows tie and take 8, the 80-pair rows of the default
@@ -875,13 +723,11 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
   const int nw = pipe_warps();
   const int owned = nw * kFusedOwnedPairs;
   *tiles = (ld_ / 2 + owned - 1) / owned;
-  const int st = pipe_stages_;
-  *smem = with_pipe_warps(nw, [&](auto w) { return pipe_smem_bytes<decltype(w)::value>(st); });
-  if (*smem > kMaxPipeSmem) throw invalid_argument("pipe_stages: the ring does not fit in shared memory");
+  *smem = pipe_smem_bytes(nw, pipe_stages_, false);
+  if (*smem > kMaxDynamicSmem) throw invalid_argument("pipe_stages: the ring does not fit in shared memory");
   if (pipe_resident_ == 0) {
     int sms = 0;
-    const size_t sm = *smem;
-    const int per_sm = with_pipe_warps(nw, [&](auto w) { return pipe_occupancy<decltype(w)::value>(sm); });
+    const int per_sm = pipe_occupancy(nw, *smem);
     PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
     pipe_resident_ = std::max(1, per_sm * sms);
   }
@@ -904,89 +750,7 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
   }
 }
 
-// ---- variant 6: variant 3 without a producer warp, 12 marching warps per CTA (fused.cuh) --------
-namespace {
-constexpr int kCoopWarps = 12;
-template <class M, int MODE>
-void launch_coop_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem, cudaStream_t st) {
-  static size_t configured = 0;  // per instantiation
-  if (configured < smem) {
-    PSV_CUDA(cudaFuncSetAttribute(fused_coop_kernel<M, MODE, kCoopWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    configured = smem;
-  }
-  fused_coop_kernel<M, MODE, kCoopWarps><<<grid, kCoopWarps * 32, smem, st>>>(fc, models, stages);
-}
-template <class M>
-void launch_coop(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
-                 cudaStream_t st) {
-  if (mode == MODE_SNAPSHOT) launch_coop_k<M, MODE_SNAPSHOT>(fc, models, grid, stages, smem, st);
-  else if (mode == MODE_ACCUMULATE) launch_coop_k<M, MODE_ACCUMULATE>(fc, models, grid, stages, smem, st);
-  else launch_coop_k<M, MODE_PLAIN>(fc, models, grid, stages, smem, st);
-}
-}  // namespace
-
-// Launch geometry of variant 6: one CTA per SM (its ring fills the shared memory), whole waves.
-void Model::coop_geometry(int batch, int mode, int *tiles, int *strip, int *stages, size_t *smem) {
-  const int owned = kCoopWarps * kFusedOwnedPairs;
-  *tiles = (ld_ / 2 + owned - 1) / owned;
-  const int arrays = mode == MODE_ACCUMULATE ? kPipeArraysCorr : kPipeArrays;
-  int st = coop_stages_;
-  while (st > 2 && pipe_smem_bytes<kCoopWarps>(st, arrays) > kMaxPipeSmem) --st;
-  *stages = st;
-  *smem = pipe_smem_bytes<kCoopWarps>(st, arrays);
-  if (fused_strip_ > 0) {
-    *strip = fused_strip_;
-    return;
-  }
-  int sms = 0;
-  PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
-  const int blocks_x = *tiles * batch;
-  const int nx = cfg_.nx;
-  for (int waves = 1;; ++waves) {
-    const int n_strips = std::max(1, waves * sms / blocks_x);
-    const int s = (nx + n_strips - 1) / n_strips;
-    if (s <= 128 || n_strips >= nx) {
-      *strip = std::max(s, 2);
-      return;
-    }
-  }
-}
-
-// ---- variant 5: two time steps per launch (pair.cuh) -------------------------------------------
-namespace {
-constexpr size_t kMaxDynamicSmem = 232448;  // 227 KB per CTA on sm_100
-
-template <class M, int MODE, int NW>
-void launch_pair_k(const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
-                   cudaStream_t st) {
-  static size_t configured = 0;  // per instantiation
-  if (configured < smem) {
-    PSV_CUDA(cudaFuncSetAttribute(fused_pair_kernel<M, MODE, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    configured = smem;
-  }
-  fused_pair_kernel<M, MODE, NW><<<grid, 2 * NW * 32, smem, st>>>(fc, models, stages);
-}
-template <class M, int NW>
-void launch_pair_m(int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages, size_t smem,
-                   cudaStream_t st) {
-  if (mode == MODE_SNAPSHOT) launch_pair_k<M, MODE_SNAPSHOT, NW>(fc, models, grid, stages, smem, st);
-  else if (mode == MODE_ACCUMULATE) launch_pair_k<M, MODE_ACCUMULATE, NW>(fc, models, grid, stages, smem, st);
-  else launch_pair_k<M, MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
-}
-template <class M>
-void launch_pair(int nw, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages,
-                 size_t smem, cudaStream_t st) {
-  if (nw == 4) launch_pair_m<M, 4>(mode, fc, models, grid, stages, smem, st);
-  else launch_pair_m<M, 6>(mode, fc, models, grid, stages, smem, st);
-}
-size_t pair_smem(int nw, int stages) {
-  return nw == 4 ? pair_smem_bytes<4>(stages) : pair_smem_bytes<6>(stages);
-}
-}  // namespace
-
-// Launch geometry of variant 5: even z-tiles over the pairs that hold real columns, and rows per
+// Launch geometry of variant 4 (two steps per launch): even z-tiles over the pairs that hold real columns, and rows per
 // CTA such that the launch is a whole number of waves (one CTA per SM: the rings fill its smem).
 void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem) {
   const int nw = pair_warps_;
@@ -1022,8 +786,8 @@ void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, si
 
 void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
   const Config &c = cfg_;
-  if (slab_ && variant_ != 2 && variant_ != 3 && variant_ != 6)
-    throw invalid_argument("A slab of a split grid runs the fused variants 2, 3 and 6 only.");
+  if (slab_ && variant_ != 2 && variant_ != 3)
+    throw invalid_argument("A slab of a split grid runs the fused variants 2 and 3 only.");
   FusedCommon fc{};
   fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, x_off_, nx_global_};
   fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
@@ -1067,10 +831,9 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
       fc.strip = fused_strip_;
     } else {  // whole waves of resident blocks, as fused_auto_strip does for variant 2
       if (fused32_resident_ == 0) {
-        int per_sm = 0, sms = 0;
-        PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused32_step_kernel<MODE_PLAIN>, 128, 0));
+        int sms = 0;
         PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
-        fused32_resident_ = std::max(1, per_sm * sms);
+        fused32_resident_ = std::max(1, fused32_occupancy() * sms);
       }
       const int blocks_x = ((fc.n_zwarps + wpb - 1) / wpb) * batch;
       fc.strip = 8;
@@ -1084,11 +847,8 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
       }
     }
     dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
-    const FusedModel32 *m32 = fused_model32_.as<FusedModel32>();
-    if (mode == MODE_SNAPSHOT) fused32_step_kernel<MODE_SNAPSHOT><<<grid, 128, 0, stream_>>>(fc, m32);
-    else if (mode == MODE_ACCUMULATE) fused32_step_kernel<MODE_ACCUMULATE><<<grid, 128, 0, stream_>>>(fc, m32);
-    else fused32_step_kernel<MODE_PLAIN><<<grid, 128, 0, stream_>>>(fc, m32);
-  } else if (variant_ == 5 && pair_step != 0) {
+    launch_fused32(mode, fc, fused_model32_.as<FusedModel32>(), grid, stream_);
+  } else if (variant_ == 4 && pair_step != 0) {
     int tiles = 0, tile_pairs = 0, strip = 0;
     size_t smem = 0;
     pair_geometry(batch, &tiles, &tile_pairs, &strip, &smem);
@@ -1096,25 +856,9 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     fc.tile_pairs = tile_pairs;
     fc.it_step = pair_step;
     dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
-    if (exact_) launch_pair<ExactMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
-    else launch_pair<FastMath>(pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
+    launch_pair(exact_, pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
     ++stat_pair_launches_;
-  } else if (variant_ == 6) {
-    int tiles = 0, strip = 0, stages = 0;
-    size_t smem = 0;
-    coop_geometry(batch, mode, &tiles, &strip, &stages, &smem);
-    fc.strip = strip;
-    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
-    if (exact_) launch_coop<ExactMath>(mode, fc, models, grid, stages, smem, stream_);
-    else launch_coop<FastMath>(mode, fc, models, grid, stages, smem, stream_);
-  } else if (variant_ == 4) {
-    int tiles = 0, strip = 0;
-    win_geometry(batch, &tiles, &strip);
-    fc.strip = strip;
-    dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
-    if (exact_) launch_win<ExactMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
-    else launch_win<FastMath>(win_config_, mode, fc, models, grid, stream_, nullptr);
-  } else if (variant_ == 3 || variant_ == 5) {
+  } else if (variant_ == 3 || variant_ == 4) {
     int tiles = 0, strip = 0;
     size_t smem = 0;
     pipe_geometry(batch, &tiles, &strip, &smem);
@@ -1123,23 +867,14 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     const int nw = pipe_warps();
     int stages = pipe_stages_;
     if (mode == MODE_ACCUMULATE) {
-      stages = with_pipe_warps(nw, [&](auto w) { return pipe_corr_stages<decltype(w)::value>(stages); });
-      const int sc = stages;
-      smem = with_pipe_warps(nw, [&](auto w) { return pipe_smem_bytes<decltype(w)::value>(sc, kPipeArraysCorr); });
+      stages = pipe_corr_stages(nw, stages);
+      smem = pipe_smem_bytes(nw, stages, true);
     }
-    const int sl = stages;
-    const size_t sb = smem;
-    with_pipe_warps(nw, [&](auto w) {
-      constexpr int NW = decltype(w)::value;
-      if (exact_) launch_pipe_m<ExactMath, NW>(mode, fc, models, grid, sl, sb, stream_);
-      else launch_pipe_m<FastMath, NW>(mode, fc, models, grid, sl, sb, stream_);
-      return 0;
-    });
+    launch_pipe(exact_, nw, mode, fc, models, grid, stages, smem, stream_);
   } else {
     const int wpb = fused_block_ / 32;
     dim3 grid((fc.n_zwarps + wpb - 1) / wpb, (c.nx + fc.strip - 1) / fc.strip, batch);
-    if (exact_) launch_fused_m<ExactMath>(mode, fc, models, grid, fused_block_, stream_);
-    else launch_fused_m<FastMath>(mode, fc, models, grid, fused_block_, stream_);
+    launch_fused_step(exact_, mode, fc, models, grid, fused_block_, stream_);
   }
   cur_ ^= 1;
   ++stat_launches_;
@@ -1189,9 +924,9 @@ struct Profiler {  // CUDA events around sampled sweep launches
 };
 }  // namespace
 
-// The fused FP64 marches (variants 2, 3, 5, 6) store receiver increments; the running sum over time
+// The fused FP64 marches (variants 2, 3, 4) store receiver increments; the running sum over time
 // is taken once after the time loop (same order, same rounding as the reference's in-loop sum).
-bool Model::receiver_increments() const { return !fp32_ && variant_ >= 2 && variant_ != 4; }
+bool Model::receiver_increments() const { return !fp32_ && variant_ >= 2; }
 
 void Model::finish_receivers(int i_shot, cudaStream_t st) {
   const Config &c = cfg_;
@@ -1211,7 +946,7 @@ std::vector<unsigned long long> Model::graph_key(int direction, int i_shot, bool
   auto n = [](long long v) { return (unsigned long long)v; };
   const ShotPlan &plan = plans_[i_shot];
   return {n(direction > 0), n(i_shot), n(store), n(variant_), n(exact_), n(fp32_), n(fused_strip_), n(fused_block_),
-          n(pipe_stages_), n(pipe_warps_), n(win_config_), n(coop_stages_), n(pdl_), n(l2_mode_), n(pair_warps_),
+          n(pipe_stages_), n(pipe_warps_), n(pdl_), n(l2_mode_), n(pair_warps_),
           n(pair_stages_), n(pair_strip_), n((long long)batch_followers_.size()), p(fused_model_.as<char>()),
           p(fused_model32_.as<char>()), p(fields_.as<char>()), n((long long)fields_.bytes()), p(fields32_.as<char>()),
           n((long long)fields32_.bytes()), p(taper_table_.as<char>()), p(rec_row_start_.as<char>()),
@@ -1333,10 +1068,10 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   for (int it = 0; it < c.nt; ++it) {
     if (variant_ >= 2) {
       const bool snap = store_fields && it % c.snapshot_interval == 0;
-      // variant 5 advances two steps per launch unless the second one has a snapshot to store
-      const bool pair = variant_ == 5 && !fp32_ && !output_wavefields && it + 1 < c.nt &&
+      // variant 4 advances two steps per launch unless the second one has a snapshot to store
+      const bool pair = variant_ == 4 && !fp32_ && !output_wavefields && it + 1 < c.nt &&
                         !(store_fields && (it + 1) % c.snapshot_interval == 0);
-      const bool sample = prof.sample(snap || (variant_ == 5 && !pair));
+      const bool sample = prof.sample(snap || (variant_ == 4 && !pair));
       if (sample) prof.mark(0);
       launch_fused(c.dt, snap ? MODE_SNAPSHOT : MODE_PLAIN, POINT_FORWARD, i_shot, it / c.snapshot_interval, it,
                    pair ? 1 : 0);
@@ -1460,9 +1195,9 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   if (variant_ >= 2 && !begun) fused_begin(i_shot, POINT_ADJOINT);
   for (int it = c.nt - 1; it >= 0; --it) {
     const bool corr = it % c.snapshot_interval == 0;
-    // variant 5 retreats two steps per launch unless the second one correlates with a snapshot
-    const bool pair = variant_ == 5 && !fp32_ && it - 1 >= 0 && (it - 1) % c.snapshot_interval != 0;
-    const bool sample = prof.sample(corr || (variant_ == 5 && !pair));
+    // variant 4 retreats two steps per launch unless the second one correlates with a snapshot
+    const bool pair = variant_ == 4 && !fp32_ && it - 1 >= 0 && (it - 1) % c.snapshot_interval != 0;
+    const bool sample = prof.sample(corr || (variant_ == 4 && !pair));
     if (variant_ >= 2) {
       if (sample) prof.mark(0);
       launch_fused(-c.dt, corr ? MODE_ACCUMULATE : MODE_PLAIN, c.nr > 0 ? POINT_ADJOINT : POINT_NONE, i_shot,
@@ -1519,8 +1254,8 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
 void Model::march_begin(int i_shot, bool adjoint, bool store_fields) {
   check_shot(i_shot);
   bind();
-  if (variant_ != 2 && variant_ != 3 && variant_ != 6)
-    throw invalid_argument("psv_march_* needs the fused variant 2, 3 or 6.");
+  if (variant_ != 2 && variant_ != 3)
+    throw invalid_argument("psv_march_* needs the fused variant 2 or 3.");
   if (march_.active) throw state_error("A march is already in progress on this model.");
   if (adjoint && snapshots_[i_shot].empty())
     throw state_error("The adjoint march needs the forward wavefield of this shot: run the stored forward march first.");
@@ -2262,10 +1997,6 @@ void Model::set_option(const std::string &name, long long v) {
   } else if (name == "fused_strip") {
     if (v < 0) throw invalid_argument("fused_strip must be >= 0 (0 = whole waves)");
     fused_strip_ = (int)v;
-  } else if (name == "win_config") {
-    if (v < 0 || v >= kWinConfigCount) throw invalid_argument("win_config out of range");
-    win_config_ = (int)v;
-    win_resident_ = 0;
   } else if (name == "fp32") {
     bind();
     if (slab_ && v) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
@@ -2277,9 +2008,6 @@ void Model::set_option(const std::string &name, long long v) {
       if (fp32_) ensure_fp32();
       zero_dynamic_fields();
     }
-  } else if (name == "coop_stages") {
-    if (v < 2 || v > 8) throw invalid_argument("coop_stages must be 2..8");
-    coop_stages_ = (int)v;
   } else if (name == "l2_persist_mb") {
     if (v < 0 || v > 120) throw invalid_argument("l2_persist_mb must be 0..120");
     l2_persist_mb_ = (int)v;
@@ -2298,10 +2026,8 @@ void Model::set_option(const std::string &name, long long v) {
     pipe_stages_ = (int)v;
     pipe_resident_ = 0;
   } else if (name == "pipe_warps") {
-    if (v != 0 && v != 3 && v != 4 && v != 8 && v != 12)
-      throw invalid_argument("pipe_warps must be 0 (auto), 3, 4, 8 or 12");
+    if (v != 0 && v != 3 && v != 4 && v != 8) throw invalid_argument("pipe_warps must be 0 (auto), 3, 4 or 8");
     pipe_warps_ = (int)v;
-    pipe_resident_ = 0;
     pipe_resident_ = 0;
   } else if (name == "pair_warps") {
     if (v != 4 && v != 6) throw invalid_argument("pair_warps must be 4 or 6");
@@ -2334,7 +2060,6 @@ long long Model::get_option(const std::string &name) const {
   if (name == "fused_strip") return fused_strip_;
   if (name == "fused_block") return fused_block_;
   if (name == "pipe_stages") return pipe_stages_;
-  if (name == "win_config") return win_config_;
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
   if (name == "pdl") return pdl_ ? 1 : 0;

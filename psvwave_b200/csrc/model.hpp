@@ -76,7 +76,7 @@ SlabSpec slab_partition(int nx_global, int rank, int nranks, int halo);
 
 class Model {
  public:
-  static constexpr int kVariantCount = 7;
+  static constexpr int kVariantCount = 5;
   explicit Model(Config cfg, int device, const SlabSpec *slab = nullptr);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
   ~Model();
@@ -183,10 +183,8 @@ class Model {
   int fused_auto_strip(int n_zwarps, int batch);
   int pipe_warps() const;
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
-  void win_geometry(int batch, int *tiles, int *strip);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
   void pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem);
-  void coop_geometry(int batch, int mode, int *tiles, int *strip, int *stages, size_t *smem);
   // Slack (in doubles) before and after the snapshot and Lame-kernel allocations: the bulk copies of
   // the correlation launches read whole row segments, which start 2 pairs before a row and may run
   // past its end by a tile's tail.
@@ -256,8 +254,6 @@ class Model {
   int fused_strip_ = 0 /* 0 = whole waves */, fused_block_ = 128;
   int fused_resident_blocks_ = 0;
   int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
-  int win_config_ = 0, win_resident_ = 0;
-  int coop_stages_ = 5;  // ring depth of variant 6
   int l2_persist_mb_ = 0;  // persisting-L2 carve-out for the medium arrays the step kernel re-reads (0 = off)
   void apply_l2_window();
   bool pdl_ = false;  // programmatic dependent launch of consecutive variant-3 step kernels

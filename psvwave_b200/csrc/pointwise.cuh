@@ -6,6 +6,8 @@
 
 #include <cuda_runtime.h>
 
+#include "fused_types.cuh"
+
 namespace psv {
 
 // ---- receiver sampling (src/fdModel.cpp:576-596) -------------------------------------------
@@ -241,6 +243,30 @@ __global__ void vector_kernel(const VectorArgs a, double *f0, double *f1, double
 __global__ void descent_axpy_kernel(double *m, const double *g, const double step, const size_t n) {
   const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) m[k] = __dsub_rn(m[k], __dmul_rn(step, g[k]));
+}
+
+// Running sum of the receiver increments the marches stored (src/fdModel.cpp:584-594): u[it] = u[it-1] + s[it],
+// one thread per trace and model (blockIdx.y), the reference's sequential order and rounding.
+__global__ void receiver_prefix_models_kernel(const FusedModel *__restrict__ models, int nr, int nt) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= 2 * nr) return;
+  const FusedModel &m = models[blockIdx.y];
+  double *u = (r < nr ? m.ux : m.uz) + (size_t)(r % nr) * nt;
+  double acc = u[0];
+  for (int it = 1; it < nt; ++it) {
+    acc = __dadd_rn(acc, u[it]);
+    u[it] = acc;
+  }
+}
+
+// double <-> float images of grid arrays (medium refresh, getters)
+__global__ void to_float_kernel(const double *__restrict__ in, float *__restrict__ out, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (float)in[i];
+}
+__global__ void to_double_kernel(const float *__restrict__ in, double *__restrict__ out, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (double)in[i];
 }
 
 }  // namespace psv

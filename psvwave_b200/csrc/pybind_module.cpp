@@ -361,6 +361,17 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
   });
   m.def("max_variant", [] { return psv_variant_count() - 1; });
   m.def("version", [] { return std::string(psv_version()); });
+  // psv_array enumerators under the reference's field names (src/fdModel.h:209-252), for _get_array
+  m.def("_array_ids", [] {
+    py::dict d;
+    const char *names[PSV_ARRAY_COUNT_] = {
+        "vx", "vz", "txx", "tzz", "txz", "lm", "la", "mu", "b_vx", "b_vz", "rho", "vp", "vs", "lambda_kernel",
+        "mu_kernel", "density_l_kernel", "vp_kernel", "vs_kernel", "density_v_kernel", "taper", "t", "stf", "moment",
+        "rtf_ux", "rtf_uz", "rtf_ux_true", "rtf_uz_true", "a_stf_ux", "a_stf_uz", "accu_vx", "accu_vz", "accu_txx",
+        "accu_tzz", "accu_txz"};
+    for (int i = 0; i < PSV_ARRAY_COUNT_; ++i) d[names[i]] = i;
+    return d;
+  });
   // additive: Monte-Carlo ensembles, one launch per time step for all models (psv_forward_batch)
   m.def(
       "forward_batch",

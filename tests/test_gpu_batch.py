@@ -13,7 +13,7 @@ from oracle.oracle import OracleModel
 pytestmark = pytest.mark.gpu
 
 KERNELS = ("lambda_kernel", "mu_kernel", "density_l_kernel")
-BATCH_VARIANTS = [dict(variant=2), dict(variant=3), dict(variant=3, pipe_warps=4), dict(variant=3, pipe_warps=8), dict(variant=4), dict(variant=5), dict(variant=6)]
+BATCH_VARIANTS = [dict(variant=2), dict(variant=3), dict(variant=3, pipe_warps=4), dict(variant=3, pipe_warps=8), dict(variant=4)]
 
 
 def fd(ini, **options):

@@ -39,7 +39,7 @@ def gradient_workflow_store(m):
     m.map_kernels_to_velocity()
 
 
-@pytest.mark.parametrize("options", [dict(), dict(exact=1), dict(variant=2), dict(pdl=1), dict(variant=6, exact=1)],
+@pytest.mark.parametrize("options", [dict(), dict(exact=1), dict(variant=2), dict(pdl=1), dict(variant=4, exact=1)],
                          ids=lambda o: "-".join(f"{k}{v}" for k, v in o.items()) or "default")
 def test_graph_replay_is_bit_identical_to_stream_launches(tmp_path, options):
     import psvwave_b200

@@ -41,14 +41,9 @@ VARIANTS = [dict(variant=0, exact=1), dict(variant=0, exact=0), dict(variant=1, 
             dict(variant=2, exact=1), dict(variant=2, exact=0), dict(variant=3, exact=1), dict(variant=3, exact=0),
             dict(variant=3, exact=1, pipe_warps=8, pipe_stages=3), dict(variant=3, exact=1, pipe_warps=3),
             dict(variant=3, exact=0, pipe_warps=4), dict(variant=2, exact=1, fused_strip=8),
-            dict(variant=4, exact=1), dict(variant=4, exact=0), dict(variant=4, exact=1, win_config=1),
-            dict(variant=4, exact=1, win_config=2), dict(variant=4, exact=1, win_config=3, fused_strip=9),
-            dict(variant=4, exact=1, win_config=4, fused_strip=13), dict(variant=4, exact=1, win_config=5),
-            dict(variant=5, exact=1), dict(variant=5, exact=0), dict(variant=5, exact=1, pair_warps=4),
-            dict(variant=5, exact=1, pair_strip=9), dict(variant=5, exact=1, pair_stages=2, pair_strip=30),
-            dict(variant=3, exact=1, pdl=1), dict(variant=3, exact=0, pdl=1, pipe_warps=4),
-            dict(variant=6, exact=1), dict(variant=6, exact=0), dict(variant=6, exact=1, coop_stages=2, fused_strip=7),
-            dict(variant=6, exact=1, coop_stages=3, fused_strip=40)]
+            dict(variant=4, exact=1), dict(variant=4, exact=0), dict(variant=4, exact=1, pair_warps=4),
+            dict(variant=4, exact=1, pair_strip=9), dict(variant=4, exact=1, pair_stages=2, pair_strip=30),
+            dict(variant=3, exact=1, pdl=1), dict(variant=3, exact=0, pdl=1, pipe_warps=4)]
 
 
 def variant_id(o):
