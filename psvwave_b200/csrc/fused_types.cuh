@@ -70,4 +70,44 @@ struct FusedModel32 {  // per-model pointers of the FP32 mode
   const double *ax, *az;
 };
 
+// ---- resident whole-loop kernel (resident.cuh) ----
+constexpr int kResidentThreads = 512;
+
+struct ResidentArgs {
+  FusedCommon c;  // geometry, constants (k.sdt carries the sign of the time direction), point lists, window
+  const FusedModel *models;
+  unsigned *flags;   // [gridDim.x * 32] zero at launch; flags[32*b] = time steps CTA b has finished
+  unsigned *abort;   // set to 1 when a wait timed out (host turns it into an error)
+  int rows;          // rows per CTA
+  int nsteps;        // nt
+  int direction;     // +1 forward, -1 adjoint
+  int store;         // forward: store snapshots every si steps
+  int si;            // snapshot interval
+  size_t grid_elems; // nx * ld (one snapshot of one field)
+  const int *op_rank;   // per row-sorted injection operation: how many earlier operations hit the same (field, point)
+  const int *rec_rank;  // per row-sorted receiver: how many earlier receivers sit on the same point
+  int op_rounds, rec_rounds;  // 1 + largest rank
+};
+
+// Shared-memory tiles of one CTA (offsets in doubles).  Every tile is preceded by 16 doubles of slack, so the
+// z-neighbour reads of a row's first / last pair stay inside the allocation (they only feed frame points, whose
+// results are discarded).
+struct ResidentLayout {
+  int pitch, rows;
+  int vx, vz, xx, zz, xz, lm, mu, b, end;
+  __host__ __device__ ResidentLayout(int ld, int r) : pitch(ld), rows(r) {
+    int off = 16 + 16;  // barrier + slack
+    vx = off; off += (r + 8) * ld + 16;
+    vz = off; off += (r + 8) * ld + 16;
+    xx = off; off += (r + 4) * ld + 16;
+    zz = off; off += (r + 4) * ld + 16;
+    xz = off; off += (r + 4) * ld + 16;
+    lm = off; off += (r + 4) * ld + 16;
+    mu = off; off += (r + 4) * ld + 16;
+    b = off; off += r * ld + 16;
+    end = off;
+  }
+  __host__ __device__ size_t bytes() const { return (size_t)end * sizeof(double); }
+};
+
 }  // namespace psv

@@ -53,4 +53,9 @@ size_t pair_smem(int nw, int stages);
 void launch_pair(bool exact, int nw, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages,
                  size_t smem, cudaStream_t st);
 
+// ---- resident whole-loop kernel for grids that fit on chip (resident.cuh) ----
+size_t resident_smem_bytes(int ld, int rows);
+int resident_max_ctas(size_t smem);  // co-resident CTAs on the current device (0: no cooperative launch / too large)
+void launch_resident(bool exact, const ResidentArgs &a, dim3 grid, int threads, size_t smem, cudaStream_t st);
+
 }  // namespace psv

@@ -4,6 +4,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iomanip>
@@ -84,6 +85,8 @@ Model::Model(Config cfg, int device, const SlabSpec *slab) : cfg_(std::move(cfg)
     cfg_.nx = slab->x1 - slab->x0;  // everything below sizes by the local row count
   }
   bind();
+  // process-wide default of the "resident" option (test suites pin the per-step kernels with PSVWAVE_RESIDENT=0)
+  if (const char *e = std::getenv("PSVWAVE_RESIDENT")) resident_ = std::max(-1, std::min(1, std::atoi(e)));
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
   PSV_CUDA(cudaEventCreate(&ev_end_));
@@ -241,6 +244,18 @@ void Model::build_plans() {
     }
     rec_row_x_.allocate(rx.size() * sizeof(int));
     copy_sync(rec_row_x_.as<int>(), rx.data(), rx.size() * sizeof(int), cudaMemcpyHostToDevice);
+    // position of every sorted receiver in the chain of receivers on its grid point (resident.cuh applies
+    // coinciding adjoint sources round by round, in receiver order)
+    std::vector<int> rank(std::max(c.nr, 1), 0);
+    std::map<std::pair<int, int>, int> seen;
+    rec_rounds_ = 1;
+    for (size_t q = 0; q < order.size(); ++q) {
+      rank[q] = seen[std::make_pair(rx[q], rz[q])]++;
+      rec_rounds_ = std::max(rec_rounds_, rank[q] + 1);
+    }
+    rec_rank_.allocate(rank.size() * sizeof(int));
+    copy_sync(rec_rank_.as<int>(), rank.data(), rank.size() * sizeof(int), cudaMemcpyHostToDevice);
+    rec_row_start_host_ = row_start;
     rec_row_start_.allocate(row_start.size() * sizeof(int));
     rec_row_z_.allocate(rz.size() * sizeof(int));
     rec_row_id_.allocate(rid.size() * sizeof(int));
@@ -304,6 +319,16 @@ void Model::build_plans() {
         rops[q] = RowOp{o.point % ld_, o.field, o.source, o.point / ld_, o.weight, o.sign, o.d4, 1.0 / o.d4};
       }
       for (int x = 0; x < c.nx; ++x) row_start[x + 1] += row_start[x];
+      std::vector<int> rank(rops.size(), 0);
+      std::map<std::pair<int, int>, int> seen;  // (field, point) -> operations so far
+      p.op_rounds = 1;
+      for (size_t q = 0; q < ops.size(); ++q) {
+        rank[q] = seen[std::make_pair(ops[order[q]].field, ops[order[q]].point)]++;
+        p.op_rounds = std::max(p.op_rounds, rank[q] + 1);
+      }
+      p.op_rank.allocate(rank.size() * sizeof(int));
+      copy_sync(p.op_rank.as<int>(), rank.data(), rank.size() * sizeof(int), cudaMemcpyHostToDevice);
+      p.op_row_start_host = row_start;
       p.row_ops.allocate(rops.size() * sizeof(RowOp));
       p.op_row_start.allocate(row_start.size() * sizeof(int));
       copy_sync(p.row_ops.as<RowOp>(), rops.data(), rops.size() * sizeof(RowOp), cudaMemcpyHostToDevice);
@@ -353,6 +378,8 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   pdl_ = o.pdl_;
   graph_ = o.graph_;
   pair_warps_ = o.pair_warps_;
+  resident_ = o.resident_;
+  resident_rows_ = o.resident_rows_;
   pair_stages_ = o.pair_stages_;
   pair_strip_ = o.pair_strip_;
   l2_persist_mb_ = o.l2_persist_mb_;
@@ -750,6 +777,14 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
   }
 }
 
+// Depth of the input ring of variant 4: the option, or (0) as many stages as fit next to the exchange ring.
+int Model::pair_stages() const {
+  if (pair_stages_ != 0) return pair_stages_;
+  int stages = 4;
+  while (stages > 2 && pair_smem(pair_warps_, stages) > kMaxDynamicSmem) --stages;
+  return stages;
+}
+
 // Launch geometry of variant 4 (two steps per launch): even z-tiles over the pairs that hold real columns, and rows per
 // CTA such that the launch is a whole number of waves (one CTA per SM: the rings fill its smem).
 void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem) {
@@ -758,14 +793,9 @@ void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, si
   const int pairs = (cfg_.nz + 1) / 2;
   *tiles = (pairs + max_tile - 1) / max_tile;
   *tile_pairs = (pairs + *tiles - 1) / *tiles;
-  int stages = pair_stages_;
-  if (stages == 0) {
-    stages = 4;
-    while (stages > 2 && pair_smem(nw, stages) > kMaxDynamicSmem) --stages;
-  }
+  const int stages = pair_stages();
   *smem = pair_smem(nw, stages);
   if (*smem > kMaxDynamicSmem) throw invalid_argument("pair_stages: the rings do not fit in shared memory");
-  pair_stages_ = stages;
   if (pair_strip_ > 0) {
     *strip = pair_strip_;
     return;
@@ -784,10 +814,9 @@ void Model::pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, si
   }
 }
 
-void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
+// Everything a step launch needs besides the per-model pointers.
+void Model::fill_fused_common(void *out, double sdt, int point_mode, int i_shot, int snap, int it) {
   const Config &c = cfg_;
-  if (slab_ && variant_ != 2 && variant_ != 3)
-    throw invalid_argument("A slab of a split grid runs the fused variants 2 and 3 only.");
   FusedCommon fc{};
   fc.g = GridShape{c.nx, c.nz, ld_, c.np_boundary, x_off_, nx_global_};
   fc.k = SweepConsts{sdt, c.dx, c.dz, 1.0 / c.dx, 1.0 / c.dz, 9.0 / 8.0, 1.0 / 24.0};
@@ -795,7 +824,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.parity = cur_;
   fc.field_stride = field_stride_;
   fc.n_zwarps = (ld_ / 2 + kFusedOwnedPairs - 1) / kFusedOwnedPairs;
-  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1 + (int)batch_followers_.size()));
+  fc.strip = 0;
   fc.tile_pairs = 0;
   fc.it_step = 0;
   fc.l2_mode = l2_mode_;
@@ -822,6 +851,16 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   fc.op_row_start = plans_[i_shot].op_row_start.as<int>();
   fc.ops = plans_[i_shot].row_ops.as<RowOp>();
   fc.stf = stf_.as<>();
+  *static_cast<FusedCommon *>(out) = fc;
+}
+
+void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step) {
+  const Config &c = cfg_;
+  if (slab_ && variant_ != 2 && variant_ != 3)
+    throw invalid_argument("A slab of a split grid runs the fused variants 2 and 3 only.");
+  FusedCommon fc{};
+  fill_fused_common(&fc, sdt, point_mode, i_shot, snap, it);
+  fc.strip = fused_strip_ > 0 ? fused_strip_ : (variant_ >= 3 ? 0 : fused_auto_strip(fc.n_zwarps, 1 + (int)batch_followers_.size()));
   const FusedModel *models = fused_model_.as<FusedModel>();
   const int batch = 1 + (int)batch_followers_.size();
   if (fp32_) {
@@ -856,7 +895,7 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
     fc.tile_pairs = tile_pairs;
     fc.it_step = pair_step;
     dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
-    launch_pair(exact_, pair_warps_, mode, fc, models, grid, pair_stages_, smem, stream_);
+    launch_pair(exact_, pair_warps_, mode, fc, models, grid, pair_stages(), smem, stream_);
     ++stat_pair_launches_;
   } else if (variant_ == 3 || variant_ == 4) {
     int tiles = 0, strip = 0;
@@ -878,6 +917,90 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   }
   cur_ ^= 1;
   ++stat_launches_;
+}
+
+// ---- resident whole-loop kernel (resident.cuh): one launch per simulate call on grids that fit on chip ----
+namespace {
+constexpr long long kResidentAutoPoints = 1 << 18;
+}  // namespace
+
+// Rows per CTA, CTAs and shared memory of the loop kernel for this grid, or false when it does not apply.
+// `forced` (option "resident" = 1) turns the reasons into errors.
+bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t *smem) {
+  const bool forced = resident_ == 1;
+  auto no = [&](const char *why) {
+    if (forced) throw invalid_argument(std::string("resident = 1: ") + why);
+    return false;
+  };
+  if (resident_ == 0) return false;
+  if (slab_) return no("not available on a slab of a split grid");
+  if (fp32_) return no("not available in the FP32 wavefield mode");
+  if (variant_ < 2) return no("needs a fused variant (>= 2)");
+  if (profile_) return no("per-launch profiling needs one launch per step");
+  if (!batch_followers_.empty()) return no("ensembles share per-step launches");
+  if (!forced && (variant_ != 3 || (long long)cfg_.nx * cfg_.nz > kResidentAutoPoints)) return false;
+  int r = resident_rows_ > 0 ? resident_rows_ : 2;
+  for (;; ++r) {
+    const size_t bytes = resident_smem_bytes(ld_, r);
+    if (bytes > kMaxDynamicSmem) return no("the strips do not fit in shared memory");
+    auto f = resident_capacity_.find(r);
+    if (f == resident_capacity_.end()) f = resident_capacity_.emplace(r, resident_max_ctas(bytes)).first;
+    const int need = (cfg_.nx + r - 1) / r;
+    if (need <= f->second) {
+      *rows = r;
+      *ctas = need;
+      *smem = bytes;
+      break;
+    }
+    if (f->second == 0) return no("cooperative launch is not available");
+    if (resident_rows_ > 0) return no("resident_rows: too many strips to be co-resident");
+  }
+  // a strip's point operations are handled one per thread
+  const std::vector<int> &ops = plans_[i_shot].op_row_start_host, &rec = rec_row_start_host_;
+  for (int x = 0; x < cfg_.nx; x += *rows) {
+    const int xe = std::min(x + *rows, cfg_.nx);
+    if ((!adjoint && ops[xe] - ops[x] > kResidentThreads) || (adjoint && rec[xe] - rec[x] > kResidentThreads))
+      return no("more point operations in one strip than threads");
+  }
+  return true;
+}
+
+void Model::run_resident(int i_shot, bool adjoint, bool store, int rows, int ctas, size_t smem) {
+  const Config &c = cfg_;
+  ResidentArgs a{};
+  const int point_mode = adjoint ? (c.nr > 0 ? POINT_ADJOINT : POINT_NONE) : POINT_FORWARD;
+  fill_fused_common(&a.c, adjoint ? -c.dt : c.dt, point_mode, i_shot, 0, 0);
+  a.c.rec_increments = 1;
+  a.models = fused_model_.as<FusedModel>();
+  const size_t flag_bytes = ((size_t)ctas * 32 + 32) * sizeof(unsigned);
+  if (resident_flags_.bytes() < flag_bytes) resident_flags_.allocate(flag_bytes);
+  PSV_CUDA(cudaMemsetAsync(resident_flags_.as<char>(), 0, flag_bytes, stream_));
+  a.flags = resident_flags_.as<unsigned>();
+  a.abort = a.flags + (size_t)ctas * 32;
+  resident_abort_word_ = a.abort;
+  a.rows = rows;
+  a.nsteps = c.nt;
+  a.direction = adjoint ? -1 : +1;
+  a.store = store ? 1 : 0;
+  a.si = c.snapshot_interval;
+  a.grid_elems = grid_elems_;
+  a.op_rank = plans_[i_shot].op_rank.as<int>();
+  a.rec_rank = rec_rank_.as<int>();
+  a.op_rounds = plans_[i_shot].op_rounds;
+  a.rec_rounds = rec_rounds_;
+  const int threads = std::min(kResidentThreads, round_up((rows + 4) * (ld_ / 2), 32));
+  launch_resident(exact_, a, dim3(ctas, 1), threads, smem, stream_);
+  cur_ = c.nt & 1;
+  ++stat_launches_;
+  stat_resident_ = ctas;
+}
+
+// After the loop kernel: a wait that timed out (a CTA never published its step) must not pass as a result.
+void Model::resident_check() {
+  unsigned abort = 0;
+  PSV_CUDA(cudaMemcpyAsync(&abort, resident_abort_word_, sizeof(unsigned), cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  if (abort) throw cuda_error("resident loop kernel: a strip waited for its neighbours longer than the spin limit");
 }
 
 namespace {
@@ -947,7 +1070,7 @@ std::vector<unsigned long long> Model::graph_key(int direction, int i_shot, bool
   const ShotPlan &plan = plans_[i_shot];
   return {n(direction > 0), n(i_shot), n(store), n(variant_), n(exact_), n(fp32_), n(fused_strip_), n(fused_block_),
           n(pipe_stages_), n(pipe_warps_), n(pdl_), n(l2_mode_), n(pair_warps_),
-          n(pair_stages_), n(pair_strip_), n((long long)batch_followers_.size()), p(fused_model_.as<char>()),
+          n(pair_stages()), n(pair_strip_), n((long long)batch_followers_.size()), p(fused_model_.as<char>()),
           p(fused_model32_.as<char>()), p(fields_.as<char>()), n((long long)fields_.bytes()), p(fields32_.as<char>()),
           n((long long)fields32_.bytes()), p(taper_table_.as<char>()), p(rec_row_start_.as<char>()),
           p(rec_row_z_.as<char>()), p(rec_row_x_.as<char>()), p(rec_row_id_.as<char>()),
@@ -1023,6 +1146,33 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
+  stat_resident_ = 0;
+  {  // grids that fit on chip: the whole loop in one launch (resident.cuh)
+    int rows = 0, ctas = 0;
+    size_t smem = 0;
+    if (!output_wavefields && resident_plan(i_shot, false, &rows, &ctas, &smem)) {
+      fused_begin(i_shot, POINT_FORWARD);
+      zero_dynamic_fields();
+      PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+      run_resident(i_shot, false, store_fields, rows, ctas, smem);
+      if (c.nr > 0) {
+        receiver_prefix_models_kernel<<<dim3(blocks_for(2 * (size_t)c.nr, 64), 1), 64, 0, stream_>>>(
+            fused_model_.as<FusedModel>(), c.nr, c.nt);
+        ++stat_launches_;
+      }
+      PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+      PSV_CUDA(cudaGetLastError());
+      resident_check();
+      float rms = 0;
+      PSV_CUDA(cudaEventElapsedTime(&rms, ev_begin_, ev_end_));
+      stat_elapsed_ms_ = rms;
+      if (verbose) {
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+        std::cout << "Seconds elapsed for forward wave simulation: " << secs << std::endl;
+      }
+      return;
+    }
+  }
   // option "graph": the loop of this (shot, store) is captured once, then replayed
   bool use_graph = graph_wanted() && !output_wavefields;
   const bool begun = use_graph;
@@ -1156,6 +1306,28 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
   const auto wall0 = std::chrono::steady_clock::now();
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
+  stat_resident_ = 0;
+  {  // grids that fit on chip: the whole loop in one launch (resident.cuh)
+    int rows = 0, ctas = 0;
+    size_t smem = 0;
+    if (resident_plan(i_shot, true, &rows, &ctas, &smem)) {
+      fused_begin(i_shot, POINT_ADJOINT);
+      zero_dynamic_fields();
+      PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
+      run_resident(i_shot, true, false, rows, ctas, smem);
+      PSV_CUDA(cudaEventRecord(ev_end_, stream_));
+      PSV_CUDA(cudaGetLastError());
+      resident_check();
+      float rms = 0;
+      PSV_CUDA(cudaEventElapsedTime(&rms, ev_begin_, ev_end_));
+      stat_elapsed_ms_ = rms;
+      if (verbose) {
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+        std::cout << "Seconds elapsed for adjoint wave simulation: " << secs << std::endl;
+      }
+      return;
+    }
+  }
   bool use_graph = graph_wanted();
   const bool begun = use_graph;
   const LoopGraph *cached = nullptr;
@@ -2014,6 +2186,12 @@ void Model::set_option(const std::string &name, long long v) {
     apply_l2_window();
   } else if (name == "pdl") {
     pdl_ = v != 0;
+  } else if (name == "resident") {
+    if (v < -1 || v > 1) throw invalid_argument("resident must be -1 (auto), 0 or 1");
+    resident_ = (int)v;
+  } else if (name == "resident_rows") {
+    if (v < 0 || v == 1) throw invalid_argument("resident_rows must be 0 (auto) or >= 2");
+    resident_rows_ = (int)v;
   } else if (name == "graph") {
     if (v < -1 || v > 1) throw invalid_argument("graph must be -1 (auto), 0 or 1");
     graph_ = (int)v;
@@ -2063,12 +2241,14 @@ long long Model::get_option(const std::string &name) const {
   if (name == "pipe_warps") return pipe_warps();
   if (name == "l2_mode") return l2_mode_;
   if (name == "pdl") return pdl_ ? 1 : 0;
+  if (name == "resident") return resident_;
+  if (name == "resident_rows") return resident_rows_;
   if (name == "graph") return graph_;
   if (name == "graphs_cached") return (long long)graphs_.size();
   if (name == "l2_persist_mb") return l2_persist_mb_;
   if (name == "fp32") return fp32_ ? 1 : 0;
   if (name == "pair_warps") return pair_warps_;
-  if (name == "pair_stages") return pair_stages_;
+  if (name == "pair_stages") return pair_stages();
   if (name == "pair_strip") return pair_strip_;
   throw invalid_argument("Unknown option '" + name + "'.");
 }
@@ -2079,6 +2259,7 @@ double Model::get_stat(const std::string &name) const {
   if (name == "stress_ms") return stat_stress_ms_;
   if (name == "velocity_ms") return stat_velocity_ms_;
   if (name == "pair_launches") return (double)stat_pair_launches_;
+  if (name == "resident_ctas") return (double)stat_resident_;
   if (name == "pitch") return ld_;
   if (name == "snapshot_bytes_per_shot") return 5.0 * n_snap_alloc_ * (double)grid_elems_ * sizeof(double);
   throw invalid_argument("Unknown statistic '" + name + "'.");

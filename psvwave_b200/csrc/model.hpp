@@ -150,6 +150,9 @@ class Model {
     DeviceBuffer ops, heads;
     int n_heads = 0;
     DeviceBuffer row_ops, op_row_start;  // the same operations bucketed by grid row (fused.cuh)
+    DeviceBuffer op_rank;                // position of a row-sorted operation in its (field, point) chain
+    int op_rounds = 1;                   // 1 + largest rank
+    std::vector<int> op_row_start_host;
   };
 
   void allocate();
@@ -184,7 +187,13 @@ class Model {
   int pipe_warps() const;
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
+  void fill_fused_common(void *out, double sdt, int point_mode, int i_shot, int snap, int it);
+  // resident whole-loop kernel (resident.cuh)
+  bool resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t *smem);
+  void run_resident(int i_shot, bool adjoint, bool store, int rows, int ctas, size_t smem);
+  void resident_check();
   void pair_geometry(int batch, int *tiles, int *tile_pairs, int *strip, size_t *smem);
+  int pair_stages() const;
   // Slack (in doubles) before and after the snapshot and Lame-kernel allocations: the bulk copies of
   // the correlation launches read whole row segments, which start 2 pairs before a row and may run
   // past its end by a tile's tail.
@@ -265,6 +274,13 @@ class Model {
     int end_cur = 0;
     long long launches = 0, pair_launches = 0;
   };
+  int resident_ = -1 /* -1 = auto (grids that fit on chip), 0 = off, 1 = required */, resident_rows_ = 0 /* 0 = auto */;
+  DeviceBuffer resident_flags_;  // one step counter per CTA (128 bytes apart) + the abort word
+  unsigned *resident_abort_word_ = nullptr;
+  std::map<int, int> resident_capacity_;  // rows per CTA -> co-resident CTAs
+  DeviceBuffer rec_rank_;
+  int rec_rounds_ = 1;
+  std::vector<int> rec_row_start_host_;
   int graph_ = -1;  // -1 = auto (small grids only, see graph_wanted), 0 = off, 1 = on
   bool graph_wanted() const;
   std::map<std::vector<unsigned long long>, LoopGraph> graphs_;
@@ -277,6 +293,7 @@ class Model {
   void drop_graphs();
   int pair_warps_ = 6, pair_stages_ = 0 /* 0 = as many as fit */, pair_strip_ = 0;
   long long stat_pair_launches_ = 0;
+  int stat_resident_ = 0;  // CTAs of the resident loop kernel in the last simulate call (0: per-step launches)
   double stat_pair_ms_ = 0;
   double stat_elapsed_ms_ = 0, stat_stress_ms_ = 0, stat_velocity_ms_ = 0;
   long long stat_launches_ = 0;
