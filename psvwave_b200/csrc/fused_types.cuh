@@ -76,7 +76,11 @@ constexpr int kResidentThreads = 512;
 struct ResidentArgs {
   FusedCommon c;  // geometry, constants (k.sdt carries the sign of the time direction), point lists, window
   const FusedModel *models;
-  unsigned *flags;   // [gridDim.x * 32] zero at launch; flags[32*b] = time steps CTA b has finished
+  // Velocity rows in flight between neighbouring strips: [2 parities][vx vz][nx][ld] packets of 16 bytes, each
+  // {low word, flag, high word, flag} of one double with flag = 1 + the time steps its producer has finished
+  // (zero at launch).  A reader polls the packet itself: no separate counters, no fences.
+  uint4 *packets;
+  unsigned flag_base;  // flags of this launch are flag_base + 1 .. flag_base + nsteps
   unsigned *abort;   // set to 1 when a wait timed out (host turns it into an error)
   int rows;          // rows per CTA
   int nsteps;        // nt
@@ -87,6 +91,7 @@ struct ResidentArgs {
   const int *op_rank;   // per row-sorted injection operation: how many earlier operations hit the same (field, point)
   const int *rec_rank;  // per row-sorted receiver: how many earlier receivers sit on the same point
   int op_rounds, rec_rounds;  // 1 + largest rank
+  long long *timing;          // optional [CTAs][8]: clock cycles thread 0 spent per phase, summed over the loop
 };
 
 // Shared-memory tiles of one CTA (offsets in doubles).  Every tile is preceded by 16 doubles of slack, so the
@@ -94,9 +99,9 @@ struct ResidentArgs {
 // results are discarded).
 struct ResidentLayout {
   int pitch, rows;
-  int vx, vz, xx, zz, xz, lm, mu, b, end;
+  int vx, vz, xx, zz, xz, lm, mu, b, tz, tr, end;
   __host__ __device__ ResidentLayout(int ld, int r) : pitch(ld), rows(r) {
-    int off = 16 + 16;  // barrier + slack
+    int off = 16;  // slack
     vx = off; off += (r + 8) * ld + 16;
     vz = off; off += (r + 8) * ld + 16;
     xx = off; off += (r + 4) * ld + 16;
@@ -105,6 +110,8 @@ struct ResidentLayout {
     lm = off; off += (r + 4) * ld + 16;
     mu = off; off += (r + 4) * ld + 16;
     b = off; off += r * ld + 16;
+    tz = off; off += ld;                      // Cerjan taper by column
+    tr = off; off += ((r + 4 + 15) / 16) * 16;  // Cerjan taper by row, rows xs-2 .. xe+1
     end = off;
   }
   __host__ __device__ size_t bytes() const { return (size_t)end * sizeof(double); }

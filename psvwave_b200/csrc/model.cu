@@ -959,7 +959,7 @@ bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t
   const std::vector<int> &ops = plans_[i_shot].op_row_start_host, &rec = rec_row_start_host_;
   for (int x = 0; x < cfg_.nx; x += *rows) {
     const int xe = std::min(x + *rows, cfg_.nx);
-    if ((!adjoint && ops[xe] - ops[x] > kResidentThreads) || (adjoint && rec[xe] - rec[x] > kResidentThreads))
+    if ((!adjoint && ops[xe] - ops[x] > kResidentThreads) || rec[xe] - rec[x] > kResidentThreads)
       return no("more point operations in one strip than threads");
   }
   return true;
@@ -972,12 +972,20 @@ void Model::run_resident(int i_shot, bool adjoint, bool store, int rows, int cta
   fill_fused_common(&a.c, adjoint ? -c.dt : c.dt, point_mode, i_shot, 0, 0);
   a.c.rec_increments = 1;
   a.models = fused_model_.as<FusedModel>();
-  const size_t flag_bytes = ((size_t)ctas * 32 + 32) * sizeof(unsigned);
-  if (resident_flags_.bytes() < flag_bytes) resident_flags_.allocate(flag_bytes);
-  PSV_CUDA(cudaMemsetAsync(resident_flags_.as<char>(), 0, flag_bytes, stream_));
-  a.flags = resident_flags_.as<unsigned>();
-  a.abort = a.flags + (size_t)ctas * 32;
+  // packets of the velocity rows in flight: [2 parities][vx vz][nx][ld] x 16 bytes + the abort word.  Flags are
+  // step counts on top of a base that grows from launch to launch, so the buffer is zeroed only when it is
+  // (re)allocated or the 32-bit flags would wrap.
+  const size_t packet_bytes = 4 * grid_elems_ * 16 + 128;
+  if (resident_packets_.bytes() < packet_bytes || resident_flag_base_ + 2ull * (unsigned)c.nt + 4 > 0xffffff00ull) {
+    PSV_CUDA(cudaStreamSynchronize(stream_));
+    resident_packets_.allocate(packet_bytes);
+    resident_flag_base_ = 0;
+  }
+  a.packets = resident_packets_.as<uint4>();
+  a.abort = reinterpret_cast<unsigned *>(resident_packets_.as<char>() + 4 * grid_elems_ * 16);
   resident_abort_word_ = a.abort;
+  a.flag_base = (unsigned)resident_flag_base_;
+  resident_flag_base_ += (unsigned)c.nt + 1;
   a.rows = rows;
   a.nsteps = c.nt;
   a.direction = adjoint ? -1 : +1;
@@ -988,6 +996,12 @@ void Model::run_resident(int i_shot, bool adjoint, bool store, int rows, int cta
   a.rec_rank = rec_rank_.as<int>();
   a.op_rounds = plans_[i_shot].op_rounds;
   a.rec_rounds = rec_rounds_;
+  a.timing = nullptr;
+  if (resident_timing_) {
+    const size_t tb = (size_t)ctas * 8 * sizeof(long long);
+    if (resident_timing_buf_.bytes() < tb) resident_timing_buf_.allocate(tb);
+    a.timing = resident_timing_buf_.as<long long>();
+  }
   const int threads = std::min(kResidentThreads, round_up((rows + 4) * (ld_ / 2), 32));
   launch_resident(exact_, a, dim3(ctas, 1), threads, smem, stream_);
   cur_ = c.nt & 1;
@@ -1001,6 +1015,19 @@ void Model::resident_check() {
   PSV_CUDA(cudaMemcpyAsync(&abort, resident_abort_word_, sizeof(unsigned), cudaMemcpyDeviceToHost, stream_));
   PSV_CUDA(cudaStreamSynchronize(stream_));
   if (abort) throw cuda_error("resident loop kernel: a strip waited for its neighbours longer than the spin limit");
+  if (resident_timing_ && stat_resident_ > 0) {  // mean / max over the CTAs of thread 0's cycles per step and phase
+    std::vector<long long> t((size_t)stat_resident_ * 8);
+    copy_sync(t.data(), resident_timing_buf_.as<long long>(), t.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+    for (int k = 0; k < 8; ++k) {
+      double sum = 0, mx = 0;
+      for (int b = 0; b < stat_resident_; ++b) {
+        sum += (double)t[(size_t)b * 8 + k];
+        mx = std::max(mx, (double)t[(size_t)b * 8 + k]);
+      }
+      stat_resident_phase_[k] = sum / stat_resident_ / std::max(cfg_.nt, 1);
+      stat_resident_phase_max_[k] = mx / std::max(cfg_.nt, 1);
+    }
+  }
 }
 
 namespace {
@@ -2189,6 +2216,8 @@ void Model::set_option(const std::string &name, long long v) {
   } else if (name == "resident") {
     if (v < -1 || v > 1) throw invalid_argument("resident must be -1 (auto), 0 or 1");
     resident_ = (int)v;
+  } else if (name == "resident_timing") {
+    resident_timing_ = v != 0;
   } else if (name == "resident_rows") {
     if (v < 0 || v == 1) throw invalid_argument("resident_rows must be 0 (auto) or >= 2");
     resident_rows_ = (int)v;
@@ -2260,6 +2289,10 @@ double Model::get_stat(const std::string &name) const {
   if (name == "velocity_ms") return stat_velocity_ms_;
   if (name == "pair_launches") return (double)stat_pair_launches_;
   if (name == "resident_ctas") return (double)stat_resident_;
+  if (name.rfind("resident_phase_max", 0) == 0 && name.size() == 19 && name[18] >= '0' && name[18] <= '7')
+    return stat_resident_phase_max_[name[18] - '0'];
+  if (name.rfind("resident_phase", 0) == 0 && name.size() == 15 && name[14] >= '0' && name[14] <= '7')
+    return stat_resident_phase_[name[14] - '0'];
   if (name == "pitch") return ld_;
   if (name == "snapshot_bytes_per_shot") return 5.0 * n_snap_alloc_ * (double)grid_elems_ * sizeof(double);
   throw invalid_argument("Unknown statistic '" + name + "'.");

@@ -275,9 +275,13 @@ class Model {
     long long launches = 0, pair_launches = 0;
   };
   int resident_ = -1 /* -1 = auto (grids that fit on chip), 0 = off, 1 = required */, resident_rows_ = 0 /* 0 = auto */;
-  DeviceBuffer resident_flags_;  // one step counter per CTA (128 bytes apart) + the abort word
+  DeviceBuffer resident_packets_;  // velocity rows in flight between strips (resident.cuh) + the abort word
+  unsigned long long resident_flag_base_ = 0;
   unsigned *resident_abort_word_ = nullptr;
   std::map<int, int> resident_capacity_;  // rows per CTA -> co-resident CTAs
+  bool resident_timing_ = false;
+  DeviceBuffer resident_timing_buf_;
+  double stat_resident_phase_[8] = {}, stat_resident_phase_max_[8] = {};
   DeviceBuffer rec_rank_;
   int rec_rounds_ = 1;
   std::vector<int> rec_row_start_host_;

@@ -3,25 +3,24 @@
 // loops src/fdModel.cpp:552-751 and :814-958).
 //
 // The grid is cut into strips of `rows` consecutive rows, one CTA per strip, all CTAs co-resident (cooperative
-// launch).  A CTA runs the WHOLE time loop for its strip.  Per time step it
-//   1. waits until the CTAs that own rows within 4 of its strip have published the previous step (one 32-bit
-//      counter per CTA in global memory, st.release / ld.acquire at gpu scope: neighbours only, no grid-wide barrier),
-//   2. pulls the old state it needs -- vx vz rows [xs-4, xe+4), txx tzz txz rows [xs-2, xe+2), each ONE contiguous
-//      block because rows are contiguous in z -- from L2 into shared memory with five bulk-asynchronous copies
-//      (cp.async.bulk + mbarrier),
-//   3. stores the snapshot (:555-572) / correlates with it (:817-861) / samples the receivers (:576-596) on its own
-//      rows from those tiles,
-//   4. updates the stresses of rows [xs-2, xe+2) in place in shared memory (the two halo rows on each side are
-//      recomputed, like the strips of fused.cuh) and, after a block barrier, the velocities of its own rows; applies
-//      moment-tensor / adjoint-source injections (:681-751, :951-958) to the new velocities in list order,
-//   5. writes its rows of the new state to the other ping-pong buffer in global memory and bumps its counter.
-// lm, mu and 1/rho of the strip stay in shared memory for the whole loop.  The arithmetic is the shared point-wise
-// code of stencil_math.cuh in the same order as every other variant, so "exact" results are bit-identical to the
-// reference and the default arithmetic matches the other variants bit for bit.
-//
-// Why this is safe without a grid barrier: state S_t lives in buffer t&1.  A CTA starts step t only after its
-// neighbours published S_t, i.e. finished step t-1 including all their reads of S_{t-1} from buffer (t+1)&1 -- the
-// buffer the CTA overwrites with S_{t+1} at the end of step t.
+// launch).  A CTA runs the WHOLE time loop for its strip out of shared memory:
+//   * resident for the whole loop: vx vz of rows [xs-4, xe+4), txx tzz txz of rows [xs-2, xe+2), lm mu of the
+//     same rows, 1/rho of the own rows, the Cerjan taper by row and by column;
+//   * per time step the stresses of rows [xs-2, xe+2) are updated in place (the two halo rows on each side are
+//     recomputed redundantly, like the strips of fused.cuh: same arithmetic on the same inputs, so they equal the
+//     owner's values bit for bit and never have to travel), then -- after a block barrier -- the velocities of the
+//     own rows, then the injections (src/fdModel.cpp:681-751, :951-958) in list order;
+//   * the ONLY data exchanged between strips are the new velocities of the own rows: every double is written as
+//     one 16-byte packet {low word, flag, high word, flag} with flag = number of finished steps (the LL protocol
+//     of NCCL), and the neighbours that need the row poll the packets themselves.  No separate counters, no memory
+//     fences, no grid-wide barrier: a step costs one L2 round trip of latency.  Packets are double-buffered by step
+//     parity; a strip overwrites buffer p only after it has consumed its neighbours' step that followed their last
+//     read of p;
+//   * snapshot store (:555-572), correlation with the stored forward field (:817-861) and receiver sampling
+//     (:576-596) act on the own rows of the tiles; the final state is written to the ordinary state arrays when the
+//     loop ends.
+// The arithmetic is the shared point-wise code of stencil_math.cuh in the same order as every other variant, so
+// "exact" results are bit-identical to the reference.
 #pragma once
 
 #include "fused.cuh"
@@ -30,22 +29,18 @@ namespace psv {
 
 constexpr unsigned kResidentSpinLimit = 1u << 22;
 
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ld_packet(const uint4 *p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
-  unsigned ok;
-  asm volatile(
-      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
+__device__ __forceinline__ void st_packet(uint4 *p, double d, unsigned flag) {
+  const unsigned lo = (unsigned)__double2loint(d), hi = (unsigned)__double2hiint(d);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(lo), "r"(flag), "r"(hi), "r"(flag)
+               : "memory");
 }
 
 template <class M>
@@ -59,35 +54,34 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
   const int ld = c.g.ld, P2 = ld >> 1, nz = c.g.nz, nx = c.g.nx;
   const int gx0 = c.g.x_off, gnx = c.g.nx_global;
   const int R = a.rows;
-  const int xs = blockIdx.x * R, xe = min(xs + R, nx);
+  const int xs = blockIdx.x * R, xe = min(xs + R, nx), own = xe - xs;
   const ResidentLayout L(ld, R);
   double2 *tvx = reinterpret_cast<double2 *>(sm + L.vx), *tvz = reinterpret_cast<double2 *>(sm + L.vz);
   double2 *txx = reinterpret_cast<double2 *>(sm + L.xx), *tzz = reinterpret_cast<double2 *>(sm + L.zz);
   double2 *txz = reinterpret_cast<double2 *>(sm + L.xz);
   double2 *tlm = reinterpret_cast<double2 *>(sm + L.lm), *tmu = reinterpret_cast<double2 *>(sm + L.mu);
   double2 *tb = reinterpret_cast<double2 *>(sm + L.b);
-  const unsigned bar = smem_u32(sm);
+  double *ttz = sm + L.tz, *ttr = sm + L.tr;
   // tile row of grid row j: velocities (j - xs + 4), stresses / lm / mu (j - xs + 2), b (j - xs)
 #define VROW(j) ((j) - xs + 4)
 #define SROW(j) ((j) - xs + 2)
 
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    s_abort = 0;
-  }
-  // the medium of the strip: resident for the whole loop
+  if (tid == 0) s_abort = 0;
+  // state S_0 = 0 everywhere; medium and taper of the strip
+  for (int i = tid; i < L.lm - L.vx; i += nthreads) sm[L.vx + i] = 0.0;
   {
     const double2 *glm = reinterpret_cast<const double2 *>(m.lm) + (long long)(xs - 2) * P2;
     const double2 *gmu = reinterpret_cast<const double2 *>(m.mu) + (long long)(xs - 2) * P2;
     const double2 *gb = reinterpret_cast<const double2 *>(m.b) + (long long)xs * P2;
-    for (int i = tid; i < (xe - xs + 4) * P2; i += nthreads) {
+    for (int i = tid; i < (own + 4) * P2; i += nthreads) {
       tlm[i] = __ldg(glm + i);
       tmu[i] = __ldg(gmu + i);
     }
-    for (int i = tid; i < (xe - xs) * P2; i += nthreads) tb[i] = __ldg(gb + i);
+    for (int i = tid; i < own * P2; i += nthreads) tb[i] = __ldg(gb + i);
+    for (int i = tid; i < ld; i += nthreads) ttz[i] = taper_axis(c.taper_table, c.g.np, i, nz);
+    for (int i = tid; i < own + 4; i += nthreads) ttr[i] = taper_axis(c.taper_table, c.g.np, gx0 + xs - 2 + i, gnx);
   }
-  // point operations of this strip (row-sorted lists: a contiguous range each)
+  // point operations of this strip (row-sorted lists: a contiguous range each); one per thread, constant over the loop
   const bool fwd = a.direction > 0;
   int rq0 = 0, rq1 = 0, oq0 = 0, oq1 = 0;
   if (c.point_mode != POINT_NONE) {
@@ -99,11 +93,6 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     oq1 = c.op_row_start[xe];
   }
   const bool inject = fwd ? oq1 > oq0 : (c.point_mode == POINT_ADJOINT && rq1 > rq0);
-  // neighbours whose rows this strip reads: owners of rows [xs-4, xe+4) other than this CTA
-  const int nb_lo = max(xs - 4, 0) / R, nb_hi = min(xe + 3, nx - 1) / R;
-  const int vrows = xe - xs + 8, srows = xe - xs + 4;
-  const unsigned vbytes = (unsigned)vrows * ld * 8u, sbytes = (unsigned)srows * ld * 8u;
-  // this thread's injection operation (forward) / receiver (adjoint): constant over the loop
   RowOp op{};
   int my_rank = -1, my_x = 0, my_z = 0;
   size_t my_trace = 0;
@@ -119,13 +108,34 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     my_z = c.rec_z[rq0 + tid];
     my_trace = (size_t)c.rec_id[rq0 + tid] * c.nt;
   }
+  // receiver sampled by this thread (forward): position and trace, constant over the loop
+  int smp_v = -1;
+  size_t smp_trace = 0;
+  if (fwd && c.point_mode == POINT_FORWARD && rq0 + tid < rq1) {
+    smp_v = VROW(c.rec_x[rq0 + tid]) * ld + c.rec_z[rq0 + tid];
+    smp_trace = (size_t)c.rec_id[rq0 + tid] * c.nt;
+  }
+  // halo rows of the velocities this strip reads from its neighbours: [xs-4, xs) and [xe, xe+4), inside the grid
+  const int lo0 = max(xs - 4, 0), hi1 = min(xe + 4, nx);
+  const int n_lo = xs - lo0, n_hi = hi1 - xe;       // rows below / above
+  const int halo_packets = 2 * (n_lo + n_hi) * nz;  // vx and vz
+  const size_t field_packets = (size_t)nx * ld;     // packets of one field in one parity buffer
+
+  // optional phase timing (option "resident_timing"): thread 0 accumulates clock64 deltas per phase
+  long long t_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long t_last = clock64();
+#define TICK(k)                      \
+  if (a.timing && tid == 0) {        \
+    const long long now = clock64(); \
+    t_acc[k] += now - t_last;        \
+    t_last = now;                    \
+  }
   __syncthreads();
 
   for (int step = 0; step < a.nsteps; ++step) {
     const int it = fwd ? step : a.nsteps - 1 - step;
-    const int p = step & 1;
     const bool snap_step = it % a.si == 0;
-    // this step's injection amplitudes: independent of the neighbours, fetched while waiting for them
+    // this step's injection amplitudes: independent of the neighbours, in flight while the halo arrives
     double inj_a = 0.0, inj_b = 0.0;
     if (my_rank >= 0) {
       if (fwd) {
@@ -135,50 +145,56 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
         inj_b = m.az[my_trace + it];
       }
     }
-    // 1. wait for the neighbours' previous step
+    // 1. the neighbours' velocities after step-1 (state S_step): poll the packets themselves
     if (step > 0) {
-      const int nb = nb_lo + tid;
-      if (nb <= nb_hi && nb != (int)blockIdx.x) {
-        const unsigned *f = a.flags + 32 * (size_t)(blockIdx.y * gridDim.x + nb);
-        unsigned spins = 0;
-        while (ld_acquire_u32(f) < (unsigned)step) {
-          if (++spins > kResidentSpinLimit || *reinterpret_cast<volatile unsigned *>(a.abort)) {
-            *reinterpret_cast<volatile unsigned *>(a.abort) = 1u;
-            s_abort = 1;
-            break;
+      const uint4 *pk = a.packets + (size_t)(step & 1) * 2 * field_packets;
+      const unsigned want = a.flag_base + (unsigned)step;
+      constexpr int U = 4;
+      for (int base = tid; base < halo_packets; base += U * nthreads) {
+        const uint4 *src[U];
+        double *dst[U];
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int idx = base + u * nthreads;
+          src[u] = nullptr;
+          dst[u] = nullptr;
+          v[u] = make_uint4(0u, 0u, 0u, 0u);
+          if (idx < halo_packets) {
+            const int rs = idx / nz, col = idx - rs * nz;  // row slot: [vx lo | vx hi | vz lo | vz hi]
+            const int per = n_lo + n_hi, f = rs >= per, r = rs - f * per;
+            const int j = r < n_lo ? lo0 + r : xe + (r - n_lo);
+            src[u] = pk + (size_t)f * field_packets + (size_t)j * ld + col;
+            dst[u] = sm + (f ? L.vz : L.vx) + VROW(j) * ld + col;
+            v[u] = ld_packet(src[u]);
           }
         }
-      }
-    }
-    __syncthreads();
-    if (s_abort) return;
-    // 2. old state of the strip + halos: five contiguous blocks, L2 -> shared memory
-    if (tid == 0) {
-      asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes (tiles, neighbours' rows) before the bulk copies
-      mbar_expect_tx(bar, 2u * vbytes + 3u * sbytes);
-      const long long voff = (long long)(xs - 4) * ld, soff = (long long)(xs - 2) * ld;
-      bulk_g2s(smem_u32(tvx), m.f[p][0] + voff, vbytes, bar);
-      bulk_g2s(smem_u32(tvz), m.f[p][1] + voff, vbytes, bar);
-      bulk_g2s(smem_u32(txx), m.f[p][2] + soff, sbytes, bar);
-      bulk_g2s(smem_u32(tzz), m.f[p][3] + soff, sbytes, bar);
-      bulk_g2s(smem_u32(txz), m.f[p][4] + soff, sbytes, bar);
-    }
-    {
-      unsigned spins = 0;
-      while (!mbar_try_wait(bar, (unsigned)(step & 1))) {
-        if (++spins > kResidentSpinLimit) {
-          *reinterpret_cast<volatile unsigned *>(a.abort) = 1u;
-          break;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (src[u] == nullptr) continue;
+          unsigned spins = 0;
+          while (v[u].y != want || v[u].w != want) {
+            if (++spins > kResidentSpinLimit) {
+              *reinterpret_cast<volatile unsigned *>(a.abort) = 1u;
+              s_abort = 1;
+              break;
+            }
+            v[u] = ld_packet(src[u]);
+          }
+          *dst[u] = __hiloint2double((int)v[u].z, (int)v[u].x);
         }
       }
+      __syncthreads();
+      if (s_abort) return;
     }
-    // 3. side effects on the state before the update, own rows
+    TICK(0);
+    // 2. side effects on the state before the update, own rows
     if (snap_step && (fwd ? a.store != 0 : true)) {
       const size_t snap_off = (size_t)(it / a.si) * a.grid_elems;
       if (fwd) {
         double2 *s = reinterpret_cast<double2 *>(m.snap + snap_off);
         const size_t fs2 = c.snap_field_stride >> 1;
-        for (int i = tid; i < (xe - xs) * P2; i += nthreads) {
+        for (int i = tid; i < own * P2; i += nthreads) {
           const size_t g = (size_t)xs * P2 + i;
           s[g] = tvx[4 * P2 + i];
           s[g + fs2] = tvz[4 * P2 + i];
@@ -215,20 +231,14 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       }
       __syncthreads();  // the in-place stress update below overwrites what these threads read
     }
-    if (fwd && c.point_mode == POINT_FORWARD) {  // receiver increments from the old velocities (prefix sum after the loop)
-      for (int q = rq0 + tid; q < rq1; q += nthreads) {
-        const int j = c.rec_x[q], z = c.rec_z[q];
-        const double *rvx = reinterpret_cast<const double *>(tvx + VROW(j) * P2), *rvz = reinterpret_cast<const double *>(tvz + VROW(j) * P2);
-        const double pvx = rvx[z], pvz = rvz[z];
-        const size_t t = (size_t)c.rec_id[q] * c.nt + it;
-        m.ux[t] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
-        m.uz[t] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
-      }
+    if (smp_v >= 0) {  // receiver increments from the old velocities (the running sum follows the loop)
+      const double pvx = sm[L.vx + smp_v], pvz = sm[L.vz + smp_v];
+      m.ux[smp_trace + it] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
+      m.uz[smp_trace + it] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
     }
-    // 4a. stresses of rows [xs-2, xe+2), in place
-    double2 *nf2 = reinterpret_cast<double2 *>(m.f[p ^ 1][2]), *nf3 = reinterpret_cast<double2 *>(m.f[p ^ 1][3]),
-            *nf4 = reinterpret_cast<double2 *>(m.f[p ^ 1][4]);
-    for (int i = tid; i < srows * P2; i += nthreads) {
+    TICK(1);
+    // 3. stresses of rows [xs-2, xe+2), in place
+    for (int i = tid; i < (own + 4) * P2; i += nthreads) {
       const int jr = i / P2, kp = i - jr * P2, j = xs - 2 + jr, z0 = 2 * kp;
       const bool rowok = gx0 + j >= 2 && gx0 + j < gnx - 2;
       const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
@@ -240,37 +250,30 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       const double2 vzL = tvz[v - 1], vzR = tvz[v + 1];
       const double2 lm = tlm[i], mu = tmu[i];
       double2 sxx = txx[i], szz = tzz[i], sxz = txz[i];
-      const double tr = taper_axis(c.taper_table, c.g.np, gx0 + j, gnx);
+      const double tr = ttr[jr];
+      const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
       if (za) {
         const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
         const double dzm_vz = diff4<M>(c.k, vz_0.x, vzL.y, vzL.x, vz_0.y);
         const double dzp_vx = diff4<M>(c.k, vx_0.y, vx_0.x, vxL.y, vxR.x);
         const double dxm_vz = diff4<M>(c.k, vz_0.x, vz_m1.x, vz_m2.x, vz_p1.x);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x,
-                         dmin2(tr, taper_axis(c.taper_table, c.g.np, z0, nz)), sxx.x, szz.x, sxz.x);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x, dmin2(tr, tz.x), sxx.x, szz.x, sxz.x);
       }
       if (zb) {
         const double dxp_vx = diff4<M>(c.k, vx_p1.y, vx_0.y, vx_m1.y, vx_p2.y);
         const double dzm_vz = diff4<M>(c.k, vz_0.y, vz_0.x, vzL.y, vzR.x);
         const double dzp_vx = diff4<M>(c.k, vxR.x, vx_0.y, vx_0.x, vxR.y);
         const double dxm_vz = diff4<M>(c.k, vz_0.y, vz_m1.y, vz_m2.y, vz_p1.y);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y,
-                         dmin2(tr, taper_axis(c.taper_table, c.g.np, z0 + 1, nz)), sxx.y, szz.y, sxz.y);
+        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y, dmin2(tr, tz.y), sxx.y, szz.y, sxz.y);
       }
       txx[i] = sxx;
       tzz[i] = szz;
       txz[i] = sxz;
     }
     __syncthreads();
-    // own rows of the new stresses -> global (also the rows the loop above skipped: they carry the old values)
-    for (int i = tid; i < (xe - xs) * P2; i += nthreads) {
-      const size_t g = (size_t)xs * P2 + i;
-      nf2[g] = txx[2 * P2 + i];
-      nf3[g] = tzz[2 * P2 + i];
-      nf4[g] = txz[2 * P2 + i];
-    }
-    // 4b. velocities of the own rows, in place
-    for (int i = tid; i < (xe - xs) * P2; i += nthreads) {
+    TICK(2);
+    // 4. velocities of the own rows, in place
+    for (int i = tid; i < own * P2; i += nthreads) {
       const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
       const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
       const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
@@ -283,31 +286,31 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       const double2 b = tb[i];
       const int v = (jr + 4) * P2 + kp;
       double2 vx = tvx[v], vz = tvz[v];
-      const double tr = taper_axis(c.taper_table, c.g.np, gx0 + x, gnx);
+      const double tr = ttr[jr + 2];
+      const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
       if (za) {
         const double dxm_txx = diff4<M>(c.k, xx_0.x, xx_m1.x, xx_m2.x, xx_p1.x);
         const double dzm_txz = diff4<M>(c.k, xz_0.x, xzL.y, xzL.x, xz_0.y);
         const double dxp_txz = diff4<M>(c.k, xz_p1.x, xz_0.x, xz_m1.x, xz_p2.x);
         const double dzp_tzz = diff4<M>(c.k, zz_0.y, zz_0.x, zzL.y, zzR.x);
-        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x,
-                           dmin2(tr, taper_axis(c.taper_table, c.g.np, z0, nz)), vx.x, vz.x);
+        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, dmin2(tr, tz.x), vx.x, vz.x);
       }
       if (zb) {
         const double dxm_txx = diff4<M>(c.k, xx_0.y, xx_m1.y, xx_m2.y, xx_p1.y);
         const double dzm_txz = diff4<M>(c.k, xz_0.y, xz_0.x, xzL.y, xzR.x);
         const double dxp_txz = diff4<M>(c.k, xz_p1.y, xz_0.y, xz_m1.y, xz_p2.y);
         const double dzp_tzz = diff4<M>(c.k, zzR.x, zz_0.y, zz_0.x, zzR.y);
-        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y,
-                           dmin2(tr, taper_axis(c.taper_table, c.g.np, z0 + 1, nz)), vx.y, vz.y);
+        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, dmin2(tr, tz.y), vx.y, vz.y);
       }
       tvx[v] = vx;
       tvz[v] = vz;
     }
-    // 4c. injections on the new velocities, in list order per target point (rank = position in the point's chain)
+    TICK(3);
+    // 5. injections on the new velocities, in list order per target point (rank = position in the point's chain)
     if (inject) {
       __syncthreads();
-      double *svx = reinterpret_cast<double *>(tvx), *svz = reinterpret_cast<double *>(tvz);
-      const double *sb = reinterpret_cast<const double *>(tb);
+      double *svx = sm + L.vx, *svz = sm + L.vz;
+      const double *sb = sm + L.b;
       if (fwd) {
         for (int round = 0; round < a.op_rounds; ++round) {
           if (my_rank == round) {
@@ -320,15 +323,14 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
           if (round + 1 < a.op_rounds) __syncthreads();
         }
       } else {
-        const int x = my_x, z = my_z;
         for (int round = 0; round < a.rec_rounds; ++round) {
           if (my_rank == round) {
-            const double bb = sb[(x - xs) * ld + z];
+            const double bb = sb[(my_x - xs) * ld + my_z];
             const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), inj_a), c.dxdz)
                                         : ((c.dt * bb) * inj_a) * c.rdxdz;
             const double az = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), inj_b), c.dxdz)
                                         : ((c.dt * bb) * inj_b) * c.rdxdz;
-            double *tx = svx + (size_t)VROW(x) * ld + z, *tz = svz + (size_t)VROW(x) * ld + z;
+            double *tx = svx + (size_t)VROW(my_x) * ld + my_z, *tz = svz + (size_t)VROW(my_x) * ld + my_z;
             *tx = __dadd_rn(*tx, ax);
             *tz = __dadd_rn(*tz, az);
           }
@@ -337,21 +339,38 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       }
     }
     __syncthreads();
-    // 5. own rows of the new velocities -> global, then publish the step
-    {
-      double2 *nf0 = reinterpret_cast<double2 *>(m.f[p ^ 1][0]), *nf1 = reinterpret_cast<double2 *>(m.f[p ^ 1][1]);
-      for (int i = tid; i < (xe - xs) * P2; i += nthreads) {
-        const size_t g = (size_t)xs * P2 + i;
-        nf0[g] = tvx[4 * P2 + i];
-        nf1[g] = tvz[4 * P2 + i];
+    TICK(4);
+    // 6. publish the new velocities of the own rows (state S_{step+1}) for the neighbours
+    if (step + 1 < a.nsteps) {
+      uint4 *pk = a.packets + (size_t)((step + 1) & 1) * 2 * field_packets;
+      const unsigned flag = a.flag_base + (unsigned)(step + 1);
+      const int per = own * nz;
+      for (int idx = tid; idx < 2 * per; idx += nthreads) {
+        const int f = idx >= per, r = idx - f * per, jr = r / nz, col = r - jr * nz;
+        const double d = sm[(f ? L.vz : L.vx) + (jr + 4) * ld + col];
+        st_packet(pk + (size_t)f * field_packets + (size_t)(xs + jr) * ld + col, d, flag);
       }
     }
-    __syncthreads();
-    if (tid == 0) {
-      __threadfence();
-      st_release_u32(a.flags + 32 * (size_t)(blockIdx.y * gridDim.x + blockIdx.x), (unsigned)(step + 1));
+    TICK(5);
+  }
+  // the final state of the own rows -> the ordinary state arrays (buffer nt & 1, where the per-step kernels leave it)
+  {
+    const int p = a.nsteps & 1;
+    double2 *f0 = reinterpret_cast<double2 *>(m.f[p][0]), *f1 = reinterpret_cast<double2 *>(m.f[p][1]);
+    double2 *f2 = reinterpret_cast<double2 *>(m.f[p][2]), *f3 = reinterpret_cast<double2 *>(m.f[p][3]);
+    double2 *f4 = reinterpret_cast<double2 *>(m.f[p][4]);
+    for (int i = tid; i < own * P2; i += nthreads) {
+      const size_t g = (size_t)xs * P2 + i;
+      f0[g] = tvx[4 * P2 + i];
+      f1[g] = tvz[4 * P2 + i];
+      f2[g] = txx[2 * P2 + i];
+      f3[g] = tzz[2 * P2 + i];
+      f4[g] = txz[2 * P2 + i];
     }
   }
+  if (a.timing && tid == 0)
+    for (int k = 0; k < 8; ++k) a.timing[8 * (size_t)(blockIdx.y * gridDim.x + blockIdx.x) + k] = t_acc[k];
+#undef TICK
 #undef VROW
 #undef SROW
 }

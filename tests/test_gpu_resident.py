@@ -67,7 +67,7 @@ def test_small_multishot_vs_reference_golden(golden, opts):
 def test_ragged_case_vs_oracle_and_per_step_kernels(tmp_path, rows):
     """Odd grid sizes, 3 shots, coinciding receivers (adjoint injection in two rounds), a receiver next to a source,
     stacked sources: every array of the path, against the oracle (exact) and the per-step default kernel (default
-    arithmetic: the same point-wise code, so bit-identical too)."""
+    arithmetic; FMA contraction may differ between the two kernels, so the tolerance applies)."""
     import psvwave_b200
     ini = str(tmp_path / "ragged.ini")
     ragged_config(ini)
@@ -88,7 +88,7 @@ def test_ragged_case_vs_oracle_and_per_step_kernels(tmp_path, rows):
     for name in ("rtf_ux", "rtf_uz", "a_stf_ux", "a_stf_uz", "accu_vx", "accu_vz", "accu_txx", "accu_tzz", "accu_txz",
                  "vx", "vz", "txx", "tzz", "txz") + KERNELS:
         close(gpu_array(me, name), o.array(name), name, True)
-        close(gpu_array(mf, name), gpu_array(ms, name), name + " (default arithmetic vs per-step kernel)", True)
+        close(gpu_array(mf, name), gpu_array(ms, name), name + " (default arithmetic vs per-step kernel)", False)
         close(gpu_array(mf, name), o.array(name), name, False)
     close(me.get_gradient_vector(), o.get_gradient_vector(), "gradient", True)
     assert me.misfit == pytest.approx(o.misfit, rel=1e-14)
