@@ -14,7 +14,8 @@
  *  - all pointers are HOST pointers owned by the caller unless the name says `device`;
  *    getters copy out, setters copy in (the reference's getters return copies too,
  *    src/psvWave.cpp:248-322);
- *  - calls are synchronous from the caller's point of view;
+ *  - calls are synchronous from the caller's point of view (exception: the simulate calls of an
+ *    object that psv_set_devices spread over several GPUs, see there);
  *  - arrays are C-contiguous float64 with the reference's shapes: grid (nx, nz) with iz
  *    fastest (src/contiguous_arrays.cpp:14-21), seismograms (n_shots, nr, nt), snapshots
  *    (n_shots, snapshots, nx, nz);
@@ -39,6 +40,7 @@ typedef struct psv_model *psv_handle;
 #define PSV_ERR_CUDA 3             /* CUDA runtime failure   -> Python RuntimeError */
 #define PSV_ERR_STATE 4            /* call order violated (e.g. adjoint without stored forward) */
 #define PSV_ERR_IO 5               /* file could not be written */
+#define PSV_ERR_NCCL 6             /* NCCL could not be loaded / a collective failed -> Python RuntimeError */
 
 const char *psv_last_error(void);
 const char *psv_version(void);
@@ -87,6 +89,29 @@ int psv_check_ini(const char *ini_path, char *summary, size_t capacity);
 int psv_set_default_device(int device);
 int psv_device_count(int *count);
 
+/* ---- several GPUs behind ONE object (no counterpart in the reference, whose
+ * parallelism is OpenMP inside each call) ------------------------------------------------------
+ * psv_set_devices(h, ids, n): the object spans the n CUDA devices ids[0..n) of this box.  The
+ * medium, the observed data and all options are replicated; shot s belongs to ids[s mod n] (a
+ * fixed map).  From then on psv_forward_simulate / psv_adjoint_simulate only QUEUE the run on the
+ * shot's GPU (one worker thread per GPU inside the handle) and return, so the reference's own
+ * user loop   for shot: forward_simulate(shot) ... for shot: adjoint_simulate(shot)
+ * (docs-source/source/typical-workflow.rst:5-13,42-59; fdModel::run_model,
+ * src/fdModel.cpp:1291-1308) keeps all GPUs busy; every call that reads a result waits for what it
+ * needs.  A failure inside a queued run is reported by the next call that waits.  Synthetics are
+ * gathered onto ids[0] device to device before the misfit (summed there, in the reference's
+ * order); the per-GPU lambda/mu/rho accumulations (src/fdModel.cpp:832-858) are summed by ONE
+ * ncclAllReduce(sum, double) over the contiguous kernel buffer, issued by whatever reads the
+ * kernels first (psv_map_kernels_to_velocity, psv_get_array of a Lame kernel, psv_write_kernels):
+ * native NCCL inside the library, no PyTorch, no launcher.  If ids[0] is not the device the object
+ * lives on, the object moves there.  n = 1 returns to a single device (stored snapshots of shots
+ * that ran elsewhere are dropped).  Monte-Carlo batches and the domain split need single-device
+ * handles.  The environment variable PSVWAVE_DEVICES ("all" or "0,1,...") applies the same call
+ * to every object at creation, for scripts that cannot be edited at all. */
+int psv_set_devices(psv_handle h, const int *device_ids, int n);
+/* *n = number of devices of the object; the first min(*n, capacity) ids are written to device_ids. */
+int psv_get_devices(psv_handle h, int *device_ids, int capacity, int *n);
+
 /* ---- the hot path ---------------------------------------------------------------------- */
 /* fdModel::forward_simulate       src/fdModel.cpp:526-787 (binding: src/psvWave.cpp:112-158) */
 int psv_forward_simulate(psv_handle h, int i_shot, int store_fields, int verbose,
@@ -118,7 +143,7 @@ typedef enum psv_int_key {
   PSV_INT_N_SOURCES, PSV_INT_N_SHOTS, PSV_INT_NR, PSV_INT_SNAPSHOT_INTERVAL,
   PSV_INT_SNAPSHOTS, PSV_INT_NX_FREE_PARAMETERS, PSV_INT_NZ_FREE_PARAMETERS,
   PSV_INT_FREE_PARAMETERS, PSV_INT_BASIS_GRIDPOINTS_X, PSV_INT_BASIS_GRIDPOINTS_Z,
-  PSV_INT_DEVICE, PSV_INT_KEY_COUNT_
+  PSV_INT_DEVICE, PSV_INT_N_DEVICES, PSV_INT_KEY_COUNT_
 } psv_int_key;
 typedef enum psv_real_key {
   PSV_REAL_DX = 0, PSV_REAL_DZ, PSV_REAL_DT, PSV_REAL_NP_FACTOR, PSV_REAL_SCALAR_RHO,
@@ -254,8 +279,10 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
  *   "variant"  which step kernels run the time loop (results are the same):
  *              0 one thread per point, two sweeps      1 x-marching two sweeps
  *              2 one fused launch per time step        3 (default) the same, fed by a TMA bulk-copy ring
- *              4 shared-memory window                  5 two time steps per launch
- *              6 variant 3 with 12 marching warps and no producer warp
+ *              4 two time steps per launch (temporal blocking experiment)
+ *   "resident" the WHOLE time loop in one cooperative launch for grids that fit in the SMs' shared memory
+ *              (resident.cuh): -1 (default) = whenever the grid fits, 0 = never, 1 = required;
+ *              "resident_rows" rows per CTA (0 = automatic)
  *   "exact"    1 = IEEE operation order of the reference (true divisions, no FMA): results are
  *              bit-identical to the reference build; 0 (default) = reciprocals + FMA (<= 1e-10)
  *   "fp32"     1 = optional single-precision wavefield mode (state, medium and snapshots in float,
@@ -268,7 +295,7 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
  *              the number of graphs held.  "pdl" 1 = programmatic dependent launch of consecutive variant-3 steps
  *   launch geometry (sweeps under profiles/): "strip" "block" (variants 0/1), "fused_strip"
  *              "fused_block" (2), "pipe_warps" "pipe_stages" "l2_mode" "l2_persist_mb" (3),
- *              "win_config" (4), "pair_warps" "pair_stages" "pair_strip" (5), "coop_stages" (6) */
+ *              "pair_warps" "pair_stages" "pair_strip" (4) */
 int psv_set_option(psv_handle h, const char *name, long long value);
 /* Number of sweep-kernel variants compiled into the library ("variant" < this). */
 int psv_variant_count(void);
@@ -277,7 +304,9 @@ int psv_get_option(psv_handle h, const char *name, long long *value);
  *   "elapsed_ms" device time of the whole time loop (CUDA events on the model's stream)
  *   "launches"   kernels launched by that call
  *   "stress_ms", "velocity_ms"  mean duration of one sampled launch (needs "profile" = 1)
- *   "pitch"      row pitch (in doubles) of the device grid arrays */
+ *   "pitch"      row pitch (in doubles) of the device grid arrays
+ *   "resident_ctas" CTAs of the resident whole-loop kernel in that call (0: per-step launches)
+ *   "devices", "allreduces", "allreduce_ms"  of an object on several GPUs (psv_set_devices) */
 int psv_get_stat(psv_handle h, const char *name, double *value);
 
 #ifdef __cplusplus

@@ -6,17 +6,34 @@
 #include <vector>
 
 #include "model.hpp"
+#include "multi.hpp"
 
 struct psv_model {
   psv::Model *m;
+  psv::DeviceGroup *g = nullptr;  // set by psv_set_devices with more than one device: `m` is then replica 0
 };
 
 namespace {
 thread_local std::string g_error;
 thread_local int g_default_device = -1;
 
+// The calling thread's current CUDA device is left as it was found (a model binds its own device inside).
+struct DeviceRestore {
+  int device = -1;
+  DeviceRestore() {
+    if (cudaGetDevice(&device) != cudaSuccess) {
+      cudaGetLastError();
+      device = -1;
+    }
+  }
+  ~DeviceRestore() {
+    if (device >= 0 && cudaSetDevice(device) != cudaSuccess) cudaGetLastError();
+  }
+};
+
 template <class F>
 int guarded(F &&f) {
+  DeviceRestore restore;
   try {
     f();
     return PSV_OK;
@@ -29,6 +46,9 @@ int guarded(F &&f) {
   } catch (const psv::cuda_error &e) {
     g_error = e.what();
     return PSV_ERR_CUDA;
+  } catch (const psv::nccl_error &e) {
+    g_error = e.what();
+    return PSV_ERR_NCCL;
   } catch (const psv::state_error &e) {
     g_error = e.what();
     return PSV_ERR_STATE;
@@ -47,6 +67,76 @@ int guarded(F &&f) {
 psv::Model &model(psv_handle h) {
   if (!h || !h->m) throw psv::invalid_argument("Null psv_handle.");
   return *h->m;
+}
+
+// The group of a multi-GPU handle, or null (also checks the handle).
+psv::DeviceGroup *group(psv_handle h) {
+  model(h);
+  return h->g;
+}
+
+void single_device_only(psv_handle h, const char *what) {
+  if (group(h))
+    throw psv::state_error(std::string(what) + " is not available on an object that spans several GPUs "
+                                                "(psv_set_devices); use a single-device handle.");
+}
+
+void set_devices(psv_handle h, const int *ids, int n) {
+  psv::Model &m = model(h);
+  if (!ids || n < 1) throw psv::invalid_argument("psv_set_devices needs at least one device.");
+  int count = 0;
+  PSV_CUDA(cudaGetDeviceCount(&count));
+  for (int i = 0; i < n; ++i)
+    if (ids[i] < 0 || ids[i] >= count) throw psv::invalid_argument("CUDA device index out of range.");
+  if (h->g) {  // back to one device first: synthetics and kernels onto the primary
+    h->g->collect();
+    delete h->g;
+    h->g = nullptr;
+  }
+  if (ids[0] != m.device()) {
+    psv::Model *moved = new psv::Model(m, ids[0], /*with_snapshots=*/true);
+    delete h->m;
+    h->m = moved;
+  }
+  if (n > 1) h->g = new psv::DeviceGroup(h->m, std::vector<int>(ids, ids + n));
+}
+
+// PSVWAVE_DEVICES = "all" | "0,1,2,...": every object created afterwards spans these GPUs, so that an unchanged
+// psvWave script (one object, a loop over shots) fills the box.
+void apply_device_environment(psv_handle h) {
+  const char *e = std::getenv("PSVWAVE_DEVICES");
+  if (!e || !*e) return;
+  std::vector<int> ids;
+  if (std::string(e) == "all") {
+    int count = 0;
+    PSV_CUDA(cudaGetDeviceCount(&count));
+    const int first = h->m->device();
+    for (int i = 0; i < count; ++i) ids.push_back((first + i) % count);
+  } else {
+    std::stringstream ss(e);
+    std::string tok;
+    while (std::getline(ss, tok, ',')) {
+      try {
+        ids.push_back(std::stoi(tok));
+      } catch (...) {
+        throw psv::invalid_argument("PSVWAVE_DEVICES must be \"all\" or a comma-separated list of device indices.");
+      }
+    }
+  }
+  if (ids.size() > 1 || (ids.size() == 1 && ids[0] != h->m->device())) set_devices(h, ids.data(), (int)ids.size());
+}
+
+psv_handle adopt(psv::Model *m) {
+  psv_handle h = new psv_model{m};
+  try {
+    apply_device_environment(h);
+  } catch (...) {
+    delete h->g;
+    delete h->m;
+    delete h;
+    throw;
+  }
+  return h;
 }
 
 int pick_device() {
@@ -94,7 +184,7 @@ int psv_create_from_ini(const char *ini_path, psv_handle *out) {
     *out = nullptr;
     psv::Config cfg = psv::config_from_ini(ini_path);
     const int dev = pick_device();
-    *out = new psv_model{new psv::Model(std::move(cfg), dev)};
+    *out = adopt(new psv::Model(std::move(cfg), dev));
   });
 }
 
@@ -187,7 +277,7 @@ int psv_create(const psv_config *c, psv_handle *out) {
     if (c->stf_folder) g.stf_folder = c->stf_folder;
     g.finalize();
     const int dev = pick_device();
-    *out = new psv_model{new psv::Model(std::move(g), dev)};
+    *out = adopt(new psv::Model(std::move(g), dev));
   });
 }
 
@@ -195,6 +285,19 @@ int psv_clone(psv_handle src, psv_handle *out) {
   return guarded([&] {
     if (!out) throw psv::invalid_argument("Null argument.");
     *out = nullptr;
+    if (psv::DeviceGroup *g = group(src)) {
+      g->drain();
+      psv_handle h = new psv_model{new psv::Model(model(src))};
+      try {
+        h->g = new psv::DeviceGroup(*g, h->m);
+      } catch (...) {
+        delete h->m;
+        delete h;
+        throw;
+      }
+      *out = h;
+      return;
+    }
     *out = new psv_model{new psv::Model(model(src))};
   });
 }
@@ -202,53 +305,96 @@ int psv_clone(psv_handle src, psv_handle *out) {
 int psv_destroy(psv_handle h) {
   return guarded([&] {
     if (!h) return;
+    delete h->g;  // joins the workers before the primary replica goes
     delete h->m;
     delete h;
   });
 }
 
+int psv_set_devices(psv_handle h, const int *device_ids, int n) {
+  return guarded([&] { set_devices(h, device_ids, n); });
+}
+int psv_get_devices(psv_handle h, int *device_ids, int capacity, int *n) {
+  return guarded([&] {
+    psv::Model &m = model(h);
+    std::vector<int> ids = h->g ? h->g->devices() : std::vector<int>{m.device()};
+    if (n) *n = (int)ids.size();
+    for (int i = 0; device_ids && i < capacity && i < (int)ids.size(); ++i) device_ids[i] = ids[i];
+  });
+}
+
 int psv_forward_simulate(psv_handle h, int i_shot, int store_fields, int verbose, int output_wavefields) {
-  return guarded([&] { model(h).forward_simulate(i_shot, store_fields != 0, verbose != 0, output_wavefields != 0); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->forward_simulate(i_shot, store_fields != 0, verbose != 0, output_wavefields != 0);
+    else model(h).forward_simulate(i_shot, store_fields != 0, verbose != 0, output_wavefields != 0);
+  });
 }
 int psv_adjoint_simulate(psv_handle h, int i_shot, int verbose) {
-  return guarded([&] { model(h).adjoint_simulate(i_shot, verbose != 0); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->adjoint_simulate(i_shot, verbose != 0);
+    else model(h).adjoint_simulate(i_shot, verbose != 0);
+  });
 }
 int psv_calculate_l2_misfit(psv_handle h, double *misfit_out) {
   return guarded([&] {
-    const double v = model(h).calculate_l2_misfit();
+    const double v = group(h) ? h->g->calculate_l2_misfit() : model(h).calculate_l2_misfit();
     if (misfit_out) *misfit_out = v;
   });
 }
 int psv_calculate_l2_misfit_shot(psv_handle h, int i_shot, double *misfit_out) {
   return guarded([&] {
-    const double v = model(h).calculate_l2_misfit_shot(i_shot);
+    const double v = group(h) ? h->g->calculate_l2_misfit_shot(i_shot) : model(h).calculate_l2_misfit_shot(i_shot);
     if (misfit_out) *misfit_out = v;
   });
 }
 int psv_calculate_l2_adjoint_sources(psv_handle h) {
-  return guarded([&] { model(h).calculate_l2_adjoint_sources(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->calculate_l2_adjoint_sources();
+    else model(h).calculate_l2_adjoint_sources();
+  });
 }
 int psv_reset_kernels(psv_handle h) {
-  return guarded([&] { model(h).reset_kernels(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->reset_kernels();
+    else model(h).reset_kernels();
+  });
 }
 int psv_map_kernels_to_velocity(psv_handle h) {
-  return guarded([&] { model(h).map_kernels_to_velocity(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->map_kernels_to_velocity();
+    else model(h).map_kernels_to_velocity();
+  });
 }
 int psv_update_from_velocity(psv_handle h) {
-  return guarded([&] { model(h).update_from_velocity(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->update_from_velocity();
+    else model(h).update_from_velocity();
+  });
 }
 int psv_run_model(psv_handle h, int verbose, int simulate_adjoint) {
-  return guarded([&] { model(h).run_model(verbose != 0, simulate_adjoint != 0); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->run_model(verbose != 0, simulate_adjoint != 0);
+    else model(h).run_model(verbose != 0, simulate_adjoint != 0);
+  });
 }
 
 int psv_get_model_vector(psv_handle h, double *out, size_t n) {
-  return guarded([&] { model(h).get_model_vector(out, n); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->get_model_vector(out, n);
+    else model(h).get_model_vector(out, n);
+  });
 }
 int psv_set_model_vector(psv_handle h, const double *in, size_t n) {
-  return guarded([&] { model(h).set_model_vector(in, n); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->set_model_vector(in, n);
+    else model(h).set_model_vector(in, n);
+  });
 }
 int psv_get_gradient_vector(psv_handle h, double *out, size_t n) {
-  return guarded([&] { model(h).get_gradient_vector(out, n); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->get_gradient_vector(out, n);
+    else model(h).get_gradient_vector(out, n);
+  });
 }
 
 int psv_get_int(psv_handle h, psv_int_key key, long long *out) {
@@ -275,6 +421,7 @@ int psv_get_int(psv_handle h, psv_int_key key, long long *out) {
       case PSV_INT_BASIS_GRIDPOINTS_X: *out = c.npx; break;
       case PSV_INT_BASIS_GRIDPOINTS_Z: *out = c.npz; break;
       case PSV_INT_DEVICE: *out = m.device(); break;
+      case PSV_INT_N_DEVICES: *out = h->g ? h->g->size() : 1; break;
       default: throw psv::invalid_argument("Unknown integer key.");
     }
   });
@@ -296,7 +443,7 @@ int psv_get_real(psv_handle h, psv_real_key key, double *out) {
       case PSV_REAL_ALPHA: *out = c.alpha; break;
       case PSV_REAL_T0: *out = c.source_timeshift; break;
       case PSV_REAL_DELAY_CYCLES_PER_SHOT: *out = c.delay_cycles_per_shot; break;
-      case PSV_REAL_MISFIT: *out = m.misfit(); break;
+      case PSV_REAL_MISFIT: *out = h->g ? h->g->misfit() : m.misfit(); break;
       default: throw psv::invalid_argument("Unknown real key.");
     }
   });
@@ -306,13 +453,22 @@ int psv_array_size(psv_handle h, psv_array which, size_t *count) {
   return guarded([&] { *count = model(h).array_size(which); });
 }
 int psv_get_array(psv_handle h, psv_array which, double *out, size_t count) {
-  return guarded([&] { model(h).get_array(which, out, count); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->get_array(which, out, count);
+    else model(h).get_array(which, out, count);
+  });
 }
 int psv_set_array(psv_handle h, psv_array which, const double *in, size_t count) {
-  return guarded([&] { model(h).set_array(which, in, count); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->set_array(which, in, count);
+    else model(h).set_array(which, in, count);
+  });
 }
 int psv_set_parameter_fields(psv_handle h, const double *vp, const double *vs, const double *rho, size_t count) {
-  return guarded([&] { model(h).set_parameter_fields(vp, vs, rho, count); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->set_parameter_fields(vp, vs, rho, count);
+    else model(h).set_parameter_fields(vp, vs, rho, count);
+  });
 }
 
 namespace {
@@ -349,19 +505,31 @@ int psv_get_index_list(psv_handle h, psv_index_list which, int *out, size_t coun
 }
 
 int psv_write_receivers(psv_handle h) {
-  return guarded([&] { model(h).write_receivers(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->write_receivers();
+    else model(h).write_receivers();
+  });
 }
 int psv_load_receivers(psv_handle h, int verbose) {
-  return guarded([&] { model(h).load_receivers(verbose != 0); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->load_receivers(verbose != 0);
+    else model(h).load_receivers(verbose != 0);
+  });
 }
 int psv_write_sources(psv_handle h) {
-  return guarded([&] { model(h).write_sources(); });
+  return guarded([&] { model(h).write_sources(); });  // host tables only
 }
 int psv_write_kernels(psv_handle h) {
-  return guarded([&] { model(h).write_kernels(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->write_kernels();
+    else model(h).write_kernels();
+  });
 }
 int psv_load_model(psv_handle h, const char *de_path, const char *vp_path, const char *vs_path, int verbose) {
-  return guarded([&] { model(h).load_model(de_path, vp_path, vs_path, verbose != 0); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->load_model(de_path, vp_path, vs_path, verbose != 0);
+    else model(h).load_model(de_path, vp_path, vs_path, verbose != 0);
+  });
 }
 int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, size_t n) {
   return guarded([&] { model(h).load_vector(path, verbose != 0, out, n); });
@@ -369,23 +537,32 @@ int psv_load_vector(psv_handle h, const char *path, int verbose, double *out, si
 
 int psv_run_gradient(psv_handle h, int release_each_shot, double *misfit_out) {
   return guarded([&] {
-    const double m = model(h).run_gradient(release_each_shot != 0);
+    const double m = group(h) ? h->g->run_gradient(release_each_shot != 0) : model(h).run_gradient(release_each_shot != 0);
     if (misfit_out) *misfit_out = m;
   });
 }
 int psv_descent_step(psv_handle h, double step_length) {
-  return guarded([&] { model(h).descent_step(step_length); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->descent_step(step_length);
+    else model(h).descent_step(step_length);
+  });
 }
 int psv_gradient_descent(psv_handle h, int iterations, double step_length, int release_each_shot,
                          double *misfits_out) {
-  return guarded([&] { model(h).gradient_descent(iterations, step_length, release_each_shot != 0, misfits_out); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->gradient_descent(iterations, step_length, release_each_shot != 0, misfits_out);
+    else model(h).gradient_descent(iterations, step_length, release_each_shot != 0, misfits_out);
+  });
 }
 
 namespace {
 std::vector<psv::Model *> batch_models(const psv_handle *handles, int n) {
   if (!handles || n < 1) throw psv::invalid_argument("Batched simulate needs at least one model.");
   std::vector<psv::Model *> v(n);
-  for (int i = 0; i < n; ++i) v[i] = &model(handles[i]);
+  for (int i = 0; i < n; ++i) {
+    single_device_only(handles[i], "A batched simulate call");
+    v[i] = &model(handles[i]);
+  }
   return v;
 }
 }  // namespace
@@ -418,7 +595,10 @@ int psv_slab_info(psv_handle h, long long out[7]) {
   return guarded([&] { model(h).slab_info(out); });
 }
 int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields) {
-  return guarded([&] { model(h).march_begin(i_shot, adjoint != 0, store_fields != 0); });
+  return guarded([&] {
+    single_device_only(h, "The domain split (psv_march_*)");
+    model(h).march_begin(i_shot, adjoint != 0, store_fields != 0);
+  });
 }
 int psv_march_steps(psv_handle h, int n, int *done) {
   return guarded([&] {
@@ -449,28 +629,43 @@ int psv_stream(psv_handle h, void **stream) {
 }
 
 int psv_release_snapshots(psv_handle h, int i_shot) {
-  return guarded([&] { model(h).release_snapshots(i_shot); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->release_snapshots(i_shot);
+    else model(h).release_snapshots(i_shot);
+  });
 }
 int psv_device_kernel_buffer(psv_handle h, void **device_ptr, size_t *count) {
-  return guarded([&] { model(h).kernel_buffer(device_ptr, count); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->kernel_buffer(device_ptr, count);
+    else model(h).kernel_buffer(device_ptr, count);
+  });
 }
 int psv_synchronize(psv_handle h) {
-  return guarded([&] { model(h).synchronize(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->synchronize();
+    else model(h).synchronize();
+  });
 }
 int psv_timer_start(psv_handle h) {
-  return guarded([&] { model(h).timer_start(); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->timer_start();
+    else model(h).timer_start();
+  });
 }
 int psv_timer_stop(psv_handle h, double *milliseconds) {
-  return guarded([&] { *milliseconds = model(h).timer_stop(); });
+  return guarded([&] { *milliseconds = group(h) ? h->g->timer_stop() : model(h).timer_stop(); });
 }
 int psv_set_option(psv_handle h, const char *name, long long value) {
-  return guarded([&] { model(h).set_option(name, value); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->set_option(name, value);
+    else model(h).set_option(name, value);
+  });
 }
 int psv_get_option(psv_handle h, const char *name, long long *value) {
   return guarded([&] { *value = model(h).get_option(name); });
 }
 int psv_get_stat(psv_handle h, const char *name, double *value) {
-  return guarded([&] { *value = model(h).get_stat(name); });
+  return guarded([&] { *value = group(h) ? h->g->get_stat(name) : model(h).get_stat(name); });
 }
 
 }  // extern "C"

@@ -343,7 +343,9 @@ void Model::build_plans() {
 }
 
 // Deep copy: every array, the stored snapshots included (src/fdModel.cpp:301-388).
-Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
+Model::Model(const Model &o) : Model(o, o.device_, true) {}
+
+Model::Model(const Model &o, int device, bool with_snapshots) : cfg_(o.cfg_), device_(device) {
   bind();
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
@@ -388,7 +390,7 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   auto dcopy = [&](const DeviceBuffer &src, DeviceBuffer &dst) {
     if (src.empty()) return;
     if (dst.bytes() != src.bytes()) dst.allocate(src.bytes());
-    copy_sync(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDeviceToDevice);
+    copy_sync(dst.as<char>(), src.as<char>(), src.bytes(), cudaMemcpyDefault);  // unified addressing: any device
   };
   const GridArray *gs[] = {&o.vp_, &o.vs_, &o.rho_, &o.vp_kernel_, &o.vs_kernel_, &o.density_v_kernel_};
   GridArray *gd[] = {&vp_, &vs_, &rho_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
@@ -407,9 +409,40 @@ Model::Model(const Model &o) : cfg_(o.cfg_), device_(o.device_) {
   dcopy(o.obs_uz_, obs_uz_);
   dcopy(o.a_stf_ux_, a_stf_ux_);
   dcopy(o.a_stf_uz_, a_stf_uz_);
-  for (int s = 0; s < cfg_.n_shots; ++s) dcopy(o.snapshots_[s], snapshots_[s]);
+  if (with_snapshots)
+    for (int s = 0; s < cfg_.n_shots; ++s) dcopy(o.snapshots_[s], snapshots_[s]);
   build_plans();
   PSV_CUDA(cudaDeviceSynchronize());
+}
+
+// ---- device-to-device transfers between the replicas of one object (psv::DeviceGroup, multi.cu) ----
+void Model::pull_shot_synthetics(const Model &src, int i_shot) {
+  check_shot(i_shot);
+  bind();
+  const size_t per_shot = (size_t)cfg_.nr * cfg_.nt, off = (size_t)i_shot * per_shot;
+  if (per_shot == 0) return;
+  PSV_CUDA(cudaMemcpyAsync(rtf_ux_.as<>() + off, src.rtf_ux_.as<>() + off, per_shot * sizeof(double), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaMemcpyAsync(rtf_uz_.as<>() + off, src.rtf_uz_.as<>() + off, per_shot * sizeof(double), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+void Model::pull_medium(const Model &src) {
+  bind();
+  const GridArray *gs[] = {&src.vp_, &src.vs_, &src.rho_};
+  GridArray *gd[] = {&vp_, &vs_, &rho_};
+  for (int i = 0; i < 3; ++i)
+    PSV_CUDA(cudaMemcpyAsync(gd[i]->buf.as<char>(), gs[i]->buf.as<char>(), gs[i]->buf.bytes(), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaMemcpyAsync(medium_.as<char>(), src.medium_.as<char>(), medium_.bytes(), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  if (fp32_) refresh_medium32();
+}
+
+void Model::pull_observed(const Model &src) {
+  bind();
+  if (obs_ux_.bytes() == 0) return;
+  PSV_CUDA(cudaMemcpyAsync(obs_ux_.as<char>(), src.obs_ux_.as<char>(), obs_ux_.bytes(), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaMemcpyAsync(obs_uz_.as<char>(), src.obs_uz_.as<char>(), obs_uz_.bytes(), cudaMemcpyDefault, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1939,27 +1972,31 @@ void Model::get_array(psv_array which, double *out, size_t count) {
     case PSV_ACCU_TXZ: {
       const int field = which - PSV_ACCU_VX;
       const size_t per_shot = (size_t)c.snapshots * grid;
-      for (int s = 0; s < c.n_shots; ++s) {
-        double *dst = out + (size_t)s * per_shot;
-        if (snapshots_[s].empty() || per_shot == 0) {
-          std::memset(dst, 0, per_shot * sizeof(double));
-        } else if (fp32_) {  // single-precision snapshots: one converted grid at a time
-          if (conv_.buf.empty()) conv_ = make_grid();
-          for (int k = 0; k < c.snapshots; ++k) {
-            const float *src = snapshots_[s].as<float>() + kBulkPad + ((size_t)field * n_snap_alloc_ + k) * grid_elems_;
-            to_double_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(src, conv_.data(), grid_elems_);
-            grid_to_host(conv_.data(), dst + (size_t)k * grid);
-          }
-        } else {
-          PSV_CUDA(cudaMemcpy2DAsync(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
-                                     c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost,
-                                     stream_));
-          PSV_CUDA(cudaStreamSynchronize(stream_));
-        }
-      }
+      for (int s = 0; s < c.n_shots; ++s) get_snapshots_shot(field, s, out + (size_t)s * per_shot);
       return;
     }
     default: throw invalid_argument("Unknown array id.");
+  }
+}
+
+void Model::get_snapshots_shot(int field, int s, double *dst) {
+  check_shot(s);
+  bind();
+  const Config &c = cfg_;
+  const size_t grid = (size_t)c.nx * c.nz, per_shot = (size_t)c.snapshots * grid;
+  if (snapshots_[s].empty() || per_shot == 0) {
+    std::memset(dst, 0, per_shot * sizeof(double));
+  } else if (fp32_) {  // single-precision snapshots: one converted grid at a time
+    if (conv_.buf.empty()) conv_ = make_grid();
+    for (int k = 0; k < c.snapshots; ++k) {
+      const float *src = snapshots_[s].as<float>() + kBulkPad + ((size_t)field * n_snap_alloc_ + k) * grid_elems_;
+      to_double_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(src, conv_.data(), grid_elems_);
+      grid_to_host(conv_.data(), dst + (size_t)k * grid);
+    }
+  } else {
+    PSV_CUDA(cudaMemcpy2DAsync(dst, c.nz * sizeof(double), snapshot_ptr(s, field, 0), ld_ * sizeof(double),
+                               c.nz * sizeof(double), (size_t)c.snapshots * c.nx, cudaMemcpyDeviceToHost, stream_));
+    PSV_CUDA(cudaStreamSynchronize(stream_));
   }
 }
 

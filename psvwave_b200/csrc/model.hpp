@@ -79,6 +79,9 @@ class Model {
   static constexpr int kVariantCount = 5;
   explicit Model(Config cfg, int device, const SlabSpec *slab = nullptr);
   Model(const Model &other);  // deep copy (src/fdModel.cpp:64-97,301-388)
+  // The same deep copy onto another device (psv_set_devices: one replica of the object per GPU); a replica made
+  // without the stored snapshots re-creates them with its own forward runs.
+  Model(const Model &other, int device, bool with_snapshots);
   ~Model();
 
   const Config &config() const { return cfg_; }
@@ -144,6 +147,13 @@ class Model {
   double get_stat(const std::string &name) const;
 
   double misfit() const { return misfit_; }
+
+  // ---- support for psv::DeviceGroup (multi.cu): one replica of the object per GPU, shots dealt round-robin ----
+  void set_misfit(double v) { misfit_ = v; }
+  void pull_shot_synthetics(const Model &src, int i_shot);  // rtf_ux / rtf_uz rows of one shot, device to device
+  void pull_medium(const Model &src);                       // vp vs rho lm mu b, device to device
+  void pull_observed(const Model &src);                     // observed seismograms of all shots, device to device
+  void get_snapshots_shot(int field, int i_shot, double *dst);  // (snapshots, nx, nz) of one shot, zeros if not stored
 
  private:
   struct ShotPlan {  // per-shot device lists for the point operations

@@ -280,6 +280,14 @@ class FdModel {
     return ms;
   }
   void synchronize() { check(psv_synchronize(h_)); }
+  void set_devices(const std::vector<int> &ids) { check(psv_set_devices(h_, ids.data(), (int)ids.size())); }
+  std::vector<int> devices() const {
+    int n = 0;
+    check(psv_get_devices(h_, nullptr, 0, &n));
+    std::vector<int> ids(n);
+    check(psv_get_devices(h_, ids.data(), n, &n));
+    return ids;
+  }
   py::tuple device_kernel_buffer() const {
     void *p = nullptr;
     size_t n = 0;
@@ -470,6 +478,10 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       .def("_timer_start", &FdModel::timer_start)
       .def("_timer_stop", &FdModel::timer_stop)
       .def("synchronize", &FdModel::synchronize)
+      .def("set_devices", &FdModel::set_devices, py::arg("device_ids"),
+           "Spread the object over several GPUs of this box: shots are dealt round-robin, simulate calls are queued "
+           "on the shot's GPU and return at once, getters wait; the kernels are summed by one NCCL all-reduce.")
+      .def("devices", &FdModel::devices)
       .def("_device_kernel_buffer", &FdModel::device_kernel_buffer)
       .def_static("_slab", &FdModel::slab, py::return_value_policy::take_ownership, py::arg("path"), py::arg("rank"),
                   py::arg("nranks"), py::arg("halo_rows"))
