@@ -72,6 +72,7 @@ struct FusedModel32 {  // per-model pointers of the FP32 mode
 
 // ---- resident whole-loop kernel (resident.cuh) ----
 constexpr int kResidentThreads = 512;
+constexpr int kResidentMaxOps = 128;  // injection operations (forward) / receivers (adjoint) of one strip
 
 struct ResidentArgs {
   FusedCommon c;  // geometry, constants (k.sdt carries the sign of the time direction), point lists, window
@@ -88,9 +89,6 @@ struct ResidentArgs {
   int store;         // forward: store snapshots every si steps
   int si;            // snapshot interval
   size_t grid_elems; // nx * ld (one snapshot of one field)
-  const int *op_rank;   // per row-sorted injection operation: how many earlier operations hit the same (field, point)
-  const int *rec_rank;  // per row-sorted receiver: how many earlier receivers sit on the same point
-  int op_rounds, rec_rounds;  // 1 + largest rank
   long long *timing;          // optional [CTAs][8]: clock cycles thread 0 spent per phase, summed over the loop
 };
 
@@ -99,7 +97,7 @@ struct ResidentArgs {
 // results are discarded).
 struct ResidentLayout {
   int pitch, rows;
-  int vx, vz, xx, zz, xz, lm, mu, b, tz, tr, end;
+  int vx, vz, xx, zz, xz, lm, mu, b, tz, tr, head, end;
   __host__ __device__ ResidentLayout(int ld, int r) : pitch(ld), rows(r) {
     int off = 16;  // slack
     vx = off; off += (r + 8) * ld + 16;
@@ -112,6 +110,7 @@ struct ResidentLayout {
     b = off; off += r * ld + 16;
     tz = off; off += ld;                      // Cerjan taper by column
     tr = off; off += ((r + 4 + 15) / 16) * 16;  // Cerjan taper by row, rows xs-2 .. xe+1
+    head = off; off += ((r * (ld / 2) + 1) / 2 + 15) / 16 * 16;  // ints: first injection of each own pair
     end = off;
   }
   __host__ __device__ size_t bytes() const { return (size_t)end * sizeof(double); }

@@ -27,7 +27,8 @@ void launch_m(const ResidentArgs &a, dim3 grid, int threads, size_t smem, cudaSt
   opt_in.ensure(resident_loop_kernel<M>, smem);
   void *args[] = {const_cast<ResidentArgs *>(&a)};
   // cooperative launch: all CTAs are guaranteed co-resident (they wait for each other inside the loop)
-  PSV_CUDA(cudaLaunchCooperativeKernel((const void *)resident_loop_kernel<M>, grid, dim3(threads), args, smem, st));
+  PSV_CUDA(cudaLaunchCooperativeKernel((const void *)resident_loop_kernel<M>, grid, dim3(threads), args, smem,
+                                       st));
 }
 }  // namespace
 

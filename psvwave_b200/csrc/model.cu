@@ -992,8 +992,9 @@ bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t
   const std::vector<int> &ops = plans_[i_shot].op_row_start_host, &rec = rec_row_start_host_;
   for (int x = 0; x < cfg_.nx; x += *rows) {
     const int xe = std::min(x + *rows, cfg_.nx);
-    if ((!adjoint && ops[xe] - ops[x] > kResidentThreads) || rec[xe] - rec[x] > kResidentThreads)
-      return no("more point operations in one strip than threads");
+    if ((!adjoint && (ops[xe] - ops[x] > kResidentMaxOps || rec[xe] - rec[x] > kResidentThreads)) ||
+        (adjoint && rec[xe] - rec[x] > kResidentMaxOps))
+      return no("too many sources / receivers in one strip");
   }
   return true;
 }
@@ -1025,10 +1026,6 @@ void Model::run_resident(int i_shot, bool adjoint, bool store, int rows, int cta
   a.store = store ? 1 : 0;
   a.si = c.snapshot_interval;
   a.grid_elems = grid_elems_;
-  a.op_rank = plans_[i_shot].op_rank.as<int>();
-  a.rec_rank = rec_rank_.as<int>();
-  a.op_rounds = plans_[i_shot].op_rounds;
-  a.rec_rounds = rec_rounds_;
   a.timing = nullptr;
   if (resident_timing_) {
     const size_t tb = (size_t)ctas * 8 * sizeof(long long);
@@ -2255,6 +2252,7 @@ void Model::set_option(const std::string &name, long long v) {
     resident_ = (int)v;
   } else if (name == "resident_timing") {
     resident_timing_ = v != 0;
+
   } else if (name == "resident_rows") {
     if (v < 0 || v == 1) throw invalid_argument("resident_rows must be 0 (auto) or >= 2");
     resident_rows_ = (int)v;

@@ -4,21 +4,23 @@
 //
 // The grid is cut into strips of `rows` consecutive rows, one CTA per strip, all CTAs co-resident (cooperative
 // launch).  A CTA runs the WHOLE time loop for its strip out of shared memory:
-//   * resident for the whole loop: vx vz of rows [xs-4, xe+4), txx tzz txz of rows [xs-2, xe+2), lm mu of the
-//     same rows, 1/rho of the own rows, the Cerjan taper by row and by column;
-//   * per time step the stresses of rows [xs-2, xe+2) are updated in place (the two halo rows on each side are
-//     recomputed redundantly, like the strips of fused.cuh: same arithmetic on the same inputs, so they equal the
-//     owner's values bit for bit and never have to travel), then -- after a block barrier -- the velocities of the
-//     own rows, then the injections (src/fdModel.cpp:681-751, :951-958) in list order;
-//   * the ONLY data exchanged between strips are the new velocities of the own rows: every double is written as
-//     one 16-byte packet {low word, flag, high word, flag} with flag = number of finished steps (the LL protocol
-//     of NCCL), and the neighbours that need the row poll the packets themselves.  No separate counters, no memory
-//     fences, no grid-wide barrier: a step costs one L2 round trip of latency.  Packets are double-buffered by step
-//     parity; a strip overwrites buffer p only after it has consumed its neighbours' step that followed their last
-//     read of p;
+//   * resident for the whole loop: vx vz of rows [xs-3, xe+3), the stress components the own velocities read --
+//     txx of rows [xs-2, xe], txz of rows [xs-1, xe+1], tzz of the own rows -- lm mu of those rows, 1/rho of the own
+//     rows, the Cerjan taper by row and by column;
+//   * per time step those stress rows are updated in place (the halo rows are recomputed redundantly, like the
+//     strips of fused.cuh: same explicitly rounded arithmetic on the same inputs, so they equal the owner's values
+//     bit for bit and never travel), then -- after a block barrier -- the velocities of the own rows; the thread that
+//     owns a point also applies the injections that hit it (src/fdModel.cpp:681-751, :951-958; per-point chains in
+//     list order) and sends the new value on its way at once;
+//   * the ONLY data exchanged between strips are the new velocities of rows within 3 of a strip edge: every double
+//     is written as one 16-byte packet {low word, flag, high word, flag} with flag = number of finished steps (the
+//     LL protocol of NCCL), and the neighbours that need the row poll the packets themselves.  No separate
+//     counters, no memory fences, no grid-wide barrier: a step costs one L2 round trip of latency.  Packets are
+//     double-buffered by step parity; a strip overwrites buffer p only after it has consumed its neighbours' step
+//     that followed their last read of p;
 //   * snapshot store (:555-572), correlation with the stored forward field (:817-861) and receiver sampling
-//     (:576-596) act on the own rows of the tiles; the final state is written to the ordinary state arrays when the
-//     loop ends.
+//     (:576-596) of the NEXT step act on the own rows right after they are published, i.e. while the neighbours'
+//     packets are in flight; the final state is written to the ordinary state arrays when the loop ends.
 // The arithmetic is the shared point-wise code of stencil_math.cuh in the same order as every other variant, so
 // "exact" results are bit-identical to the reference.
 #pragma once
@@ -48,6 +50,9 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
   extern __shared__ __align__(128) unsigned char psv_smem[];
   double *sm = reinterpret_cast<double *>(psv_smem);
   __shared__ int s_abort;
+  // injection operations of the strip: per-point chains (list order), static data, this step's amplitudes
+  __shared__ int s_next[kResidentMaxOps], s_meta[kResidentMaxOps];  // meta: bit 0 = z parity, 1 = vz, 2 = subtract
+  __shared__ double s_amp[kResidentMaxOps], s_amp2[kResidentMaxOps], s_d4[kResidentMaxOps], s_rd4[kResidentMaxOps];
   const FusedCommon &c = a.c;
   const FusedModel &m = a.models[blockIdx.y];
   const int tid = threadIdx.x, nthreads = blockDim.x;
@@ -62,6 +67,7 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
   double2 *tlm = reinterpret_cast<double2 *>(sm + L.lm), *tmu = reinterpret_cast<double2 *>(sm + L.mu);
   double2 *tb = reinterpret_cast<double2 *>(sm + L.b);
   double *ttz = sm + L.tz, *ttr = sm + L.tr;
+  int *head = reinterpret_cast<int *>(sm + L.head);  // first operation of the chain of own pair (jr, kp), or -1
   // tile row of grid row j: velocities (j - xs + 4), stresses / lm / mu (j - xs + 2), b (j - xs)
 #define VROW(j) ((j) - xs + 4)
 #define SROW(j) ((j) - xs + 2)
@@ -77,11 +83,14 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       tlm[i] = __ldg(glm + i);
       tmu[i] = __ldg(gmu + i);
     }
-    for (int i = tid; i < own * P2; i += nthreads) tb[i] = __ldg(gb + i);
+    for (int i = tid; i < own * P2; i += nthreads) {
+      tb[i] = __ldg(gb + i);
+      head[i] = -1;
+    }
     for (int i = tid; i < ld; i += nthreads) ttz[i] = taper_axis(c.taper_table, c.g.np, i, nz);
     for (int i = tid; i < own + 4; i += nthreads) ttr[i] = taper_axis(c.taper_table, c.g.np, gx0 + xs - 2 + i, gnx);
   }
-  // point operations of this strip (row-sorted lists: a contiguous range each); one per thread, constant over the loop
+  // point operations of this strip (row-sorted lists: a contiguous range each)
   const bool fwd = a.direction > 0;
   int rq0 = 0, rq1 = 0, oq0 = 0, oq1 = 0;
   if (c.point_mode != POINT_NONE) {
@@ -92,21 +101,39 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     oq0 = c.op_row_start[xs];
     oq1 = c.op_row_start[xe];
   }
-  const bool inject = fwd ? oq1 > oq0 : (c.point_mode == POINT_ADJOINT && rq1 > rq0);
-  RowOp op{};
-  int my_rank = -1, my_x = 0, my_z = 0;
-  size_t my_trace = 0;
-  if (fwd) {
-    if (oq0 + tid < oq1) {
-      op = c.ops[oq0 + tid];
-      my_rank = a.op_rank[oq0 + tid];
+  // injections: forward = this shot's moment-tensor operations, adjoint = the receivers (adjoint sources)
+  const int n_inj = fwd ? oq1 - oq0 : (c.point_mode == POINT_ADJOINT ? rq1 - rq0 : 0);
+  double my_weight = 0.0;  // forward: moment entry of operation `tid`
+  size_t my_trace = 0;     // row of stf (forward) / of the adjoint sources (adjoint) of injection `tid`
+  int my_item = -1;
+  if (tid < n_inj) {
+    int x, z, meta;
+    if (fwd) {
+      const RowOp op = c.ops[oq0 + tid];
+      x = op.x;
+      z = op.z;
+      meta = (z & 1) | (op.field ? 2 : 0) | (op.sign > 0 ? 0 : 4);
+      my_weight = op.weight;
       my_trace = (size_t)op.source * c.nt;
+      s_d4[tid] = op.d4;
+      s_rd4[tid] = op.rd4;
+    } else {
+      x = c.rec_x[rq0 + tid];
+      z = c.rec_z[rq0 + tid];
+      meta = z & 1;
+      my_trace = (size_t)c.rec_id[rq0 + tid] * c.nt;
     }
-  } else if (c.point_mode == POINT_ADJOINT && rq0 + tid < rq1) {
-    my_rank = a.rec_rank[rq0 + tid];
-    my_x = c.rec_x[rq0 + tid];
-    my_z = c.rec_z[rq0 + tid];
-    my_trace = (size_t)c.rec_id[rq0 + tid] * c.nt;
+    s_meta[tid] = meta;
+    my_item = (x - xs) * P2 + (z >> 1);
+  }
+  __syncthreads();
+  // chains in list order: walk the list backwards, every operation becomes the head of its point's chain
+  for (int q = n_inj - 1; q >= 0; --q) {
+    if (tid == q) {
+      s_next[q] = head[my_item];
+      head[my_item] = q;
+    }
+    __syncthreads();
   }
   // receiver sampled by this thread (forward): position and trace, constant over the loop
   int smp_v = -1;
@@ -115,11 +142,26 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     smp_v = VROW(c.rec_x[rq0 + tid]) * ld + c.rec_z[rq0 + tid];
     smp_trace = (size_t)c.rec_id[rq0 + tid] * c.nt;
   }
-  // halo rows of the velocities this strip reads from its neighbours: [xs-4, xs) and [xe, xe+4), inside the grid
-  const int lo0 = max(xs - 4, 0), hi1 = min(xe + 4, nx);
+  // halo rows of the velocities this strip reads from its neighbours: [xs-3, xs) and [xe, xe+3), inside the grid
+  const int lo0 = max(xs - 3, 0), hi1 = min(xe + 3, nx);
   const int n_lo = xs - lo0, n_hi = hi1 - xe;       // rows below / above
   const int halo_packets = 2 * (n_lo + n_hi) * nz;  // vx and vz
   const size_t field_packets = (size_t)nx * ld;     // packets of one field in one parity buffer
+  // packet `idx` of the halo: offset inside a parity buffer and the tile element it lands in
+  auto locate = [&](int idx, int &src, int &dst) {
+    const int rs = idx / nz, col = idx - rs * nz;  // row slot: [vx lo | vx hi | vz lo | vz hi]
+    const int per = n_lo + n_hi, f = rs >= per, r = rs - f * per;
+    const int j = r < n_lo ? lo0 + r : xe + (r - n_lo);
+    src = (int)(f * field_packets) + j * ld + col;
+    dst = (f ? L.vz : L.vx) + VROW(j) * ld + col;
+  };
+  constexpr int U = 4;  // packets a thread keeps in flight; their places are fixed for the whole loop
+  int p_src[U], p_dst[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    p_src[u] = p_dst[u] = -1;
+    if (tid + u * nthreads < halo_packets) locate(tid + u * nthreads, p_src[u], p_dst[u]);
+  }
 
   // optional phase timing (option "resident_timing"): thread 0 accumulates clock64 deltas per phase
   long long t_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -130,66 +172,10 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     t_acc[k] += now - t_last;        \
     t_last = now;                    \
   }
-  __syncthreads();
 
-  for (int step = 0; step < a.nsteps; ++step) {
-    const int it = fwd ? step : a.nsteps - 1 - step;
-    const bool snap_step = it % a.si == 0;
-    // this step's injection amplitudes: independent of the neighbours, in flight while the halo arrives
-    double inj_a = 0.0, inj_b = 0.0;
-    if (my_rank >= 0) {
-      if (fwd) {
-        inj_a = c.stf[my_trace + it];
-      } else {
-        inj_a = m.ax[my_trace + it];
-        inj_b = m.az[my_trace + it];
-      }
-    }
-    // 1. the neighbours' velocities after step-1 (state S_step): poll the packets themselves
-    if (step > 0) {
-      const uint4 *pk = a.packets + (size_t)(step & 1) * 2 * field_packets;
-      const unsigned want = a.flag_base + (unsigned)step;
-      constexpr int U = 4;
-      for (int base = tid; base < halo_packets; base += U * nthreads) {
-        const uint4 *src[U];
-        double *dst[U];
-        uint4 v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int idx = base + u * nthreads;
-          src[u] = nullptr;
-          dst[u] = nullptr;
-          v[u] = make_uint4(0u, 0u, 0u, 0u);
-          if (idx < halo_packets) {
-            const int rs = idx / nz, col = idx - rs * nz;  // row slot: [vx lo | vx hi | vz lo | vz hi]
-            const int per = n_lo + n_hi, f = rs >= per, r = rs - f * per;
-            const int j = r < n_lo ? lo0 + r : xe + (r - n_lo);
-            src[u] = pk + (size_t)f * field_packets + (size_t)j * ld + col;
-            dst[u] = sm + (f ? L.vz : L.vx) + VROW(j) * ld + col;
-            v[u] = ld_packet(src[u]);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (src[u] == nullptr) continue;
-          unsigned spins = 0;
-          while (v[u].y != want || v[u].w != want) {
-            if (++spins > kResidentSpinLimit) {
-              *reinterpret_cast<volatile unsigned *>(a.abort) = 1u;
-              s_abort = 1;
-              break;
-            }
-            v[u] = ld_packet(src[u]);
-          }
-          *dst[u] = __hiloint2double((int)v[u].z, (int)v[u].x);
-        }
-      }
-      __syncthreads();
-      if (s_abort) return;
-    }
-    TICK(0);
-    // 2. side effects on the state before the update, own rows
-    if (snap_step && (fwd ? a.store != 0 : true)) {
+  // Side effects of time index `it` on the state BEFORE that step's update, own rows only.
+  auto side_effects = [&](int it) {
+    if (it % a.si == 0 && (fwd ? a.store != 0 : true)) {
       const size_t snap_off = (size_t)(it / a.si) * a.grid_elems;
       if (fwd) {
         double2 *s = reinterpret_cast<double2 *>(m.snap + snap_off);
@@ -229,129 +215,185 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
           *(reinterpret_cast<double2 *>(m.k_mu) + g) = km;
         }
       }
-      __syncthreads();  // the in-place stress update below overwrites what these threads read
     }
     if (smp_v >= 0) {  // receiver increments from the old velocities (the running sum follows the loop)
       const double pvx = sm[L.vx + smp_v], pvz = sm[L.vz + smp_v];
       m.ux[smp_trace + it] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
       m.uz[smp_trace + it] = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
     }
-    TICK(1);
-    // 3. stresses of rows [xs-2, xe+2), in place
+  };
+
+  __syncthreads();
+  side_effects(fwd ? 0 : a.nsteps - 1);
+
+  for (int step = 0; step < a.nsteps; ++step) {
+    const int it = fwd ? step : a.nsteps - 1 - step;
+    // this step's injection amplitudes: independent of the neighbours, in flight while the halo arrives
+    if (tid < n_inj) {
+      if (fwd) {
+        s_amp[tid] = __dmul_rn(__dmul_rn(my_weight, c.stf[my_trace + it]), c.dt);
+      } else {
+        s_amp[tid] = m.ax[my_trace + it];
+        s_amp2[tid] = m.az[my_trace + it];
+      }
+    }
+    // 1. the neighbours' velocities after step-1 (state S_step): poll the packets themselves
+    if (step > 0) {
+      const uint4 *pk = a.packets + (size_t)(step & 1) * 2 * field_packets;
+      const unsigned want = a.flag_base + (unsigned)step;
+      auto settle = [&](const uint4 *src, uint4 v, double *dst) {
+        unsigned spins = 0;
+        while (v.y != want || v.w != want) {
+          if (++spins > kResidentSpinLimit) {
+            *reinterpret_cast<volatile unsigned *>(a.abort) = 1u;
+            s_abort = 1;
+            break;
+          }
+          v = ld_packet(src);
+        }
+        *dst = __hiloint2double((int)v.z, (int)v.x);
+      };
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (p_src[u] >= 0) v[u] = ld_packet(pk + p_src[u]);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (p_src[u] >= 0) settle(pk + p_src[u], v[u], sm + p_dst[u]);
+      for (int idx = tid + U * nthreads; idx < halo_packets; idx += nthreads) {  // wide grids: the rest, one by one
+        int src, dst;
+        locate(idx, src, dst);
+        settle(pk + src, ld_packet(pk + src), sm + dst);
+      }
+    }
+    __syncthreads();
+    if (s_abort) return;
+    TICK(0);
+    // 2. the stress components the own velocities read, in place: txx rows [xs-2, xe], tzz own rows, txz rows
+    //    [xs-1, xe+1]
     for (int i = tid; i < (own + 4) * P2; i += nthreads) {
       const int jr = i / P2, kp = i - jr * P2, j = xs - 2 + jr, z0 = 2 * kp;
       const bool rowok = gx0 + j >= 2 && gx0 + j < gnx - 2;
       const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
       if (!rowok || !(za || zb)) continue;  // frame rows / pad pairs keep their values
-      const int v = (jr + 2) * P2 + kp;     // velocity-tile index of (j, kp)
-      const double2 vx_m1 = tvx[v - P2], vx_0 = tvx[v], vx_p1 = tvx[v + P2], vx_p2 = tvx[v + 2 * P2];
-      const double2 vxL = tvx[v - 1], vxR = tvx[v + 1];
-      const double2 vz_m2 = tvz[v - 2 * P2], vz_m1 = tvz[v - P2], vz_0 = tvz[v], vz_p1 = tvz[v + P2];
-      const double2 vzL = tvz[v - 1], vzR = tvz[v + 1];
-      const double2 lm = tlm[i], mu = tmu[i];
-      double2 sxx = txx[i], szz = tzz[i], sxz = txz[i];
+      const bool do_xx = jr <= own + 2, do_zz = jr >= 2 && jr < own + 2, do_xz = jr >= 1;
+      const int v = (jr + 2) * P2 + kp;  // velocity-tile index of (j, kp)
       const double tr = ttr[jr];
       const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
-      if (za) {
-        const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
-        const double dzm_vz = diff4<M>(c.k, vz_0.x, vzL.y, vzL.x, vz_0.y);
-        const double dzp_vx = diff4<M>(c.k, vx_0.y, vx_0.x, vxL.y, vxR.x);
-        const double dxm_vz = diff4<M>(c.k, vz_0.x, vz_m1.x, vz_m2.x, vz_p1.x);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.x, mu.x, dmin2(tr, tz.x), sxx.x, szz.x, sxz.x);
+      const double tpa = dmin2(tr, tz.x), tpb = dmin2(tr, tz.y);
+      const double2 lm = tlm[i], mu = tmu[i];
+      if (do_xx) {  // D+x vx and D-z vz feed txx and tzz
+        const double2 vx_m1 = tvx[v - P2], vx_0 = tvx[v], vx_p1 = tvx[v + P2], vx_p2 = tvx[v + 2 * P2];
+        const double2 vz_0 = tvz[v], vzL = tvz[v - 1], vzR = tvz[v + 1];
+        double2 sxx = txx[i];
+        double2 szz = do_zz ? tzz[i] : make_double2(0.0, 0.0);
+        if (za) {
+          const double dxp_vx = diff4<M>(c.k, vx_p1.x, vx_0.x, vx_m1.x, vx_p2.x);
+          const double dzm_vz = diff4<M>(c.k, vz_0.x, vzL.y, vzL.x, vz_0.y);
+          sxx.x = stress_txx<M>(c.k, dxp_vx, dzm_vz, lm.x, mu.x, tpa, sxx.x);
+          if (do_zz) szz.x = stress_tzz<M>(c.k, dxp_vx, dzm_vz, lm.x, mu.x, tpa, szz.x);
+        }
+        if (zb) {
+          const double dxp_vx = diff4<M>(c.k, vx_p1.y, vx_0.y, vx_m1.y, vx_p2.y);
+          const double dzm_vz = diff4<M>(c.k, vz_0.y, vz_0.x, vzL.y, vzR.x);
+          sxx.y = stress_txx<M>(c.k, dxp_vx, dzm_vz, lm.y, mu.y, tpb, sxx.y);
+          if (do_zz) szz.y = stress_tzz<M>(c.k, dxp_vx, dzm_vz, lm.y, mu.y, tpb, szz.y);
+        }
+        txx[i] = sxx;
+        if (do_zz) tzz[i] = szz;
       }
-      if (zb) {
-        const double dxp_vx = diff4<M>(c.k, vx_p1.y, vx_0.y, vx_m1.y, vx_p2.y);
-        const double dzm_vz = diff4<M>(c.k, vz_0.y, vz_0.x, vzL.y, vzR.x);
-        const double dzp_vx = diff4<M>(c.k, vxR.x, vx_0.y, vx_0.x, vxR.y);
-        const double dxm_vz = diff4<M>(c.k, vz_0.y, vz_m1.y, vz_m2.y, vz_p1.y);
-        stress_update<M>(c.k, dxp_vx, dzm_vz, dzp_vx, dxm_vz, lm.y, mu.y, dmin2(tr, tz.y), sxx.y, szz.y, sxz.y);
+      if (do_xz) {  // D+z vx and D-x vz feed txz
+        const double2 vx_0 = tvx[v], vxL = tvx[v - 1], vxR = tvx[v + 1];
+        const double2 vz_m2 = tvz[v - 2 * P2], vz_m1 = tvz[v - P2], vz_0 = tvz[v], vz_p1 = tvz[v + P2];
+        double2 sxz = txz[i];
+        if (za) {
+          const double dzp_vx = diff4<M>(c.k, vx_0.y, vx_0.x, vxL.y, vxR.x);
+          const double dxm_vz = diff4<M>(c.k, vz_0.x, vz_m1.x, vz_m2.x, vz_p1.x);
+          sxz.x = stress_txz<M>(c.k, dzp_vx, dxm_vz, mu.x, tpa, sxz.x);
+        }
+        if (zb) {
+          const double dzp_vx = diff4<M>(c.k, vxR.x, vx_0.y, vx_0.x, vxR.y);
+          const double dxm_vz = diff4<M>(c.k, vz_0.y, vz_m1.y, vz_m2.y, vz_p1.y);
+          sxz.y = stress_txz<M>(c.k, dzp_vx, dxm_vz, mu.y, tpb, sxz.y);
+        }
+        txz[i] = sxz;
       }
-      txx[i] = sxx;
-      tzz[i] = szz;
-      txz[i] = sxz;
+    }
+    __syncthreads();
+    TICK(1);
+    // 3. velocities of the own rows, in place; injections by the owner of the point; new edge rows sent at once
+    {
+      const bool publish = step + 1 < a.nsteps;
+      uint4 *pk = a.packets + (size_t)((step + 1) & 1) * 2 * field_packets;
+      const unsigned flag = a.flag_base + (unsigned)(step + 1);
+      for (int i = tid; i < own * P2; i += nthreads) {
+        const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
+        const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
+        const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
+        const int v = (jr + 4) * P2 + kp;
+        double2 vx = tvx[v], vz = tvz[v];
+        const double2 b = tb[i];
+        if (rowok && (za || zb)) {
+          const int s = (jr + 2) * P2 + kp;  // stress-tile index of (x, kp)
+          const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
+          const double2 xz_m1 = txz[s - P2], xz_0 = txz[s], xz_p1 = txz[s + P2], xz_p2 = txz[s + 2 * P2];
+          const double2 xzL = txz[s - 1], xzR = txz[s + 1];
+          const double2 zz_0 = tzz[s], zzL = tzz[s - 1], zzR = tzz[s + 1];
+          const double tr = ttr[jr + 2];
+          const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
+          if (za) {
+            const double dxm_txx = diff4<M>(c.k, xx_0.x, xx_m1.x, xx_m2.x, xx_p1.x);
+            const double dzm_txz = diff4<M>(c.k, xz_0.x, xzL.y, xzL.x, xz_0.y);
+            const double dxp_txz = diff4<M>(c.k, xz_p1.x, xz_0.x, xz_m1.x, xz_p2.x);
+            const double dzp_tzz = diff4<M>(c.k, zz_0.y, zz_0.x, zzL.y, zzR.x);
+            velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, dmin2(tr, tz.x), vx.x, vz.x);
+          }
+          if (zb) {
+            const double dxm_txx = diff4<M>(c.k, xx_0.y, xx_m1.y, xx_m2.y, xx_p1.y);
+            const double dzm_txz = diff4<M>(c.k, xz_0.y, xz_0.x, xzL.y, xzR.x);
+            const double dxp_txz = diff4<M>(c.k, xz_p1.y, xz_0.y, xz_m1.y, xz_p2.y);
+            const double dzp_tzz = diff4<M>(c.k, zzR.x, zz_0.y, zz_0.x, zzR.y);
+            velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, dmin2(tr, tz.y), vx.y, vz.y);
+          }
+        }
+        for (int q = head[i]; q >= 0; q = s_next[q]) {  // this pair's injections, in list order
+          const int meta = s_meta[q];
+          const double bb = (meta & 1) ? b.y : b.x;
+          if (fwd) {
+            const double amp = M::kExact ? __ddiv_rn(__dmul_rn(s_amp[q], bb), s_d4[q])
+                                         : __dmul_rn(__dmul_rn(s_amp[q], bb), s_rd4[q]);
+            double &t = (meta & 2) ? ((meta & 1) ? vz.y : vz.x) : ((meta & 1) ? vx.y : vx.x);
+            t = (meta & 4) ? __dsub_rn(t, amp) : __dadd_rn(t, amp);
+          } else {
+            const double dtb = __dmul_rn(c.dt, bb);
+            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(dtb, s_amp[q]), c.dxdz)
+                                        : __dmul_rn(__dmul_rn(dtb, s_amp[q]), c.rdxdz);
+            const double az = M::kExact ? __ddiv_rn(__dmul_rn(dtb, s_amp2[q]), c.dxdz)
+                                        : __dmul_rn(__dmul_rn(dtb, s_amp2[q]), c.rdxdz);
+            double &tx = (meta & 1) ? vx.y : vx.x, &tzv = (meta & 1) ? vz.y : vz.x;
+            tx = __dadd_rn(tx, ax);
+            tzv = __dadd_rn(tzv, az);
+          }
+        }
+        tvx[v] = vx;
+        tvz[v] = vz;
+        if (publish && (jr < 3 || jr >= own - 3) && z0 < nz) {  // rows a neighbour reads (state S_{step+1})
+          uint4 *px = pk + (size_t)x * ld + z0, *pz = px + field_packets;
+          st_packet(px, vx.x, flag);
+          st_packet(pz, vz.x, flag);
+          if (z0 + 1 < nz) {
+            st_packet(px + 1, vx.y, flag);
+            st_packet(pz + 1, vz.y, flag);
+          }
+        }
+      }
     }
     __syncthreads();
     TICK(2);
-    // 4. velocities of the own rows, in place
-    for (int i = tid; i < own * P2; i += nthreads) {
-      const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
-      const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
-      const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
-      if (!rowok || !(za || zb)) continue;
-      const int s = (jr + 2) * P2 + kp;  // stress-tile index of (x, kp)
-      const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
-      const double2 xz_m1 = txz[s - P2], xz_0 = txz[s], xz_p1 = txz[s + P2], xz_p2 = txz[s + 2 * P2];
-      const double2 xzL = txz[s - 1], xzR = txz[s + 1];
-      const double2 zz_0 = tzz[s], zzL = tzz[s - 1], zzR = tzz[s + 1];
-      const double2 b = tb[i];
-      const int v = (jr + 4) * P2 + kp;
-      double2 vx = tvx[v], vz = tvz[v];
-      const double tr = ttr[jr + 2];
-      const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
-      if (za) {
-        const double dxm_txx = diff4<M>(c.k, xx_0.x, xx_m1.x, xx_m2.x, xx_p1.x);
-        const double dzm_txz = diff4<M>(c.k, xz_0.x, xzL.y, xzL.x, xz_0.y);
-        const double dxp_txz = diff4<M>(c.k, xz_p1.x, xz_0.x, xz_m1.x, xz_p2.x);
-        const double dzp_tzz = diff4<M>(c.k, zz_0.y, zz_0.x, zzL.y, zzR.x);
-        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, dmin2(tr, tz.x), vx.x, vz.x);
-      }
-      if (zb) {
-        const double dxm_txx = diff4<M>(c.k, xx_0.y, xx_m1.y, xx_m2.y, xx_p1.y);
-        const double dzm_txz = diff4<M>(c.k, xz_0.y, xz_0.x, xzL.y, xzR.x);
-        const double dxp_txz = diff4<M>(c.k, xz_p1.y, xz_0.y, xz_m1.y, xz_p2.y);
-        const double dzp_tzz = diff4<M>(c.k, zzR.x, zz_0.y, zz_0.x, zzR.y);
-        velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, dmin2(tr, tz.y), vx.y, vz.y);
-      }
-      tvx[v] = vx;
-      tvz[v] = vz;
-    }
+    // 4. what the next step does to its starting state (snapshot, correlation, receiver samples): own rows, while
+    //    the packets travel
+    if (step + 1 < a.nsteps) side_effects(fwd ? step + 1 : a.nsteps - 2 - step);
     TICK(3);
-    // 5. injections on the new velocities, in list order per target point (rank = position in the point's chain)
-    if (inject) {
-      __syncthreads();
-      double *svx = sm + L.vx, *svz = sm + L.vz;
-      const double *sb = sm + L.b;
-      if (fwd) {
-        for (int round = 0; round < a.op_rounds; ++round) {
-          if (my_rank == round) {
-            const double base = __dmul_rn(__dmul_rn(op.weight, inj_a), c.dt);
-            const double bb = sb[(op.x - xs) * ld + op.z];
-            const double amp = M::kExact ? __ddiv_rn(__dmul_rn(base, bb), op.d4) : (base * bb) * op.rd4;
-            double *t = (op.field == 0 ? svx : svz) + (size_t)VROW(op.x) * ld + op.z;
-            *t = op.sign > 0 ? __dadd_rn(*t, amp) : __dsub_rn(*t, amp);
-          }
-          if (round + 1 < a.op_rounds) __syncthreads();
-        }
-      } else {
-        for (int round = 0; round < a.rec_rounds; ++round) {
-          if (my_rank == round) {
-            const double bb = sb[(my_x - xs) * ld + my_z];
-            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), inj_a), c.dxdz)
-                                        : ((c.dt * bb) * inj_a) * c.rdxdz;
-            const double az = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), inj_b), c.dxdz)
-                                        : ((c.dt * bb) * inj_b) * c.rdxdz;
-            double *tx = svx + (size_t)VROW(my_x) * ld + my_z, *tz = svz + (size_t)VROW(my_x) * ld + my_z;
-            *tx = __dadd_rn(*tx, ax);
-            *tz = __dadd_rn(*tz, az);
-          }
-          if (round + 1 < a.rec_rounds) __syncthreads();
-        }
-      }
-    }
-    __syncthreads();
-    TICK(4);
-    // 6. publish the new velocities of the own rows (state S_{step+1}) for the neighbours
-    if (step + 1 < a.nsteps) {
-      uint4 *pk = a.packets + (size_t)((step + 1) & 1) * 2 * field_packets;
-      const unsigned flag = a.flag_base + (unsigned)(step + 1);
-      const int per = own * nz;
-      for (int idx = tid; idx < 2 * per; idx += nthreads) {
-        const int f = idx >= per, r = idx - f * per, jr = r / nz, col = r - jr * nz;
-        const double d = sm[(f ? L.vz : L.vx) + (jr + 4) * ld + col];
-        st_packet(pk + (size_t)f * field_packets + (size_t)(xs + jr) * ld + col, d, flag);
-      }
-    }
-    TICK(5);
   }
   // the final state of the own rows -> the ordinary state arrays (buffer nt & 1, where the per-step kernels leave it)
   {

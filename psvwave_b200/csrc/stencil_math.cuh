@@ -39,10 +39,12 @@ struct SweepConsts {
   double c1, c2;    // 9/8, 1/24 (src/fdModel.h:201-202)
 };
 
-// Staggered 4th-order difference: c1*(a - b) + c2*(c - d).
+// Staggered 4th-order difference: c1*(a - b) + c2*(c - d).  The default arithmetic spells its FMAs out, so that
+// every kernel (and every call site inside one) rounds the same way whatever the compiler would have contracted.
 template <class M>
 __device__ __forceinline__ double diff4(const SweepConsts &k, double a, double b, double c, double d) {
-  return M::add(M::mul(k.c1, M::sub(a, b)), M::mul(k.c2, M::sub(c, d)));
+  if (M::kExact) return M::add(M::mul(k.c1, M::sub(a, b)), M::mul(k.c2, M::sub(c, d)));
+  return __fma_rn(k.c1, __dsub_rn(a, b), __dmul_rn(k.c2, __dsub_rn(c, d)));
 }
 
 // Cerjan taper value of grid point (ix, iz): table[min(np, 1 + distance to nearest edge)]
@@ -55,28 +57,45 @@ __device__ __forceinline__ double taper_at(const double *__restrict__ table, int
   return __ldg(table + d);
 }
 
-// Stress update of one point (src/fdModel.cpp:615-642).  la = lm - 2*mu is recomputed with
-// the operation update_from_velocity uses (src/fdModel.cpp:1046), so it equals the
-// reference's stored `la` bit for bit and the array need not be read.
+// Stress update of one point (src/fdModel.cpp:615-642), one component at a time (the resident loop kernel updates
+// only the components a halo row is read for).  la = lm - 2*mu is recomputed with the operation
+// update_from_velocity uses (src/fdModel.cpp:1046), so it equals the reference's stored `la` bit for bit and the
+// array need not be read.
 //   dxp_vx = D+x vx, dzm_vz = D-z vz, dzp_vx = D+z vx, dxm_vz = D-x vz
+template <class M>
+__device__ __forceinline__ double stress_txx(const SweepConsts &k, double dxp_vx, double dzm_vz, double lm, double mu,
+                                             double tp, double txx) {
+  const double la = M::sub(lm, M::mul(2.0, mu));
+  if (M::kExact)
+    return M::mul(tp, M::add(txx, M::mul(k.sdt, M::add(M::div(M::mul(lm, dxp_vx), k.dx),
+                                                        M::div(M::mul(la, dzm_vz), k.dz)))));
+  const double ex = __dmul_rn(dxp_vx, k.rdx), ez = __dmul_rn(dzm_vz, k.rdz);
+  return __dmul_rn(tp, __fma_rn(k.sdt, __fma_rn(lm, ex, __dmul_rn(la, ez)), txx));
+}
+template <class M>
+__device__ __forceinline__ double stress_tzz(const SweepConsts &k, double dxp_vx, double dzm_vz, double lm, double mu,
+                                             double tp, double tzz) {
+  const double la = M::sub(lm, M::mul(2.0, mu));
+  if (M::kExact)
+    return M::mul(tp, M::add(tzz, M::mul(k.sdt, M::add(M::div(M::mul(la, dxp_vx), k.dx),
+                                                        M::div(M::mul(lm, dzm_vz), k.dz)))));
+  const double ex = __dmul_rn(dxp_vx, k.rdx), ez = __dmul_rn(dzm_vz, k.rdz);
+  return __dmul_rn(tp, __fma_rn(k.sdt, __fma_rn(la, ex, __dmul_rn(lm, ez)), tzz));
+}
+template <class M>
+__device__ __forceinline__ double stress_txz(const SweepConsts &k, double dzp_vx, double dxm_vz, double mu, double tp,
+                                             double txz) {
+  if (M::kExact)
+    return M::mul(tp, M::add(txz, M::mul(M::mul(k.sdt, mu), M::add(M::div(dzp_vx, k.dz), M::div(dxm_vz, k.dx)))));
+  return __dmul_rn(tp, __fma_rn(__dmul_rn(k.sdt, mu), __fma_rn(dzp_vx, k.rdz, __dmul_rn(dxm_vz, k.rdx)), txz));
+}
 template <class M>
 __device__ __forceinline__ void stress_update(const SweepConsts &k, double dxp_vx, double dzm_vz,
                                               double dzp_vx, double dxm_vz, double lm, double mu,
                                               double tp, double &txx, double &tzz, double &txz) {
-  const double la = M::sub(lm, M::mul(2.0, mu));
-  if (M::kExact) {
-    txx = M::mul(tp, M::add(txx, M::mul(k.sdt, M::add(M::div(M::mul(lm, dxp_vx), k.dx),
-                                                       M::div(M::mul(la, dzm_vz), k.dz)))));
-    tzz = M::mul(tp, M::add(tzz, M::mul(k.sdt, M::add(M::div(M::mul(la, dxp_vx), k.dx),
-                                                       M::div(M::mul(lm, dzm_vz), k.dz)))));
-    txz = M::mul(tp, M::add(txz, M::mul(M::mul(k.sdt, mu),
-                                        M::add(M::div(dzp_vx, k.dz), M::div(dxm_vz, k.dx)))));
-  } else {
-    const double ex = dxp_vx * k.rdx, ez = dzm_vz * k.rdz;
-    txx = tp * (txx + k.sdt * (lm * ex + la * ez));
-    tzz = tp * (tzz + k.sdt * (la * ex + lm * ez));
-    txz = tp * (txz + (k.sdt * mu) * (dzp_vx * k.rdz + dxm_vz * k.rdx));
-  }
+  txx = stress_txx<M>(k, dxp_vx, dzm_vz, lm, mu, tp, txx);
+  tzz = stress_tzz<M>(k, dxp_vx, dzm_vz, lm, mu, tp, tzz);
+  txz = stress_txz<M>(k, dzp_vx, dxm_vz, mu, tp, txz);
 }
 
 // Velocity update of one point (src/fdModel.cpp:661-676); b = 1/rho (b_vx == b_vz).
@@ -90,9 +109,9 @@ __device__ __forceinline__ void velocity_update(const SweepConsts &k, double dxm
     vx = M::mul(tp, M::add(vx, M::mul(bs, M::add(M::div(dxm_txx, k.dx), M::div(dzm_txz, k.dz)))));
     vz = M::mul(tp, M::add(vz, M::mul(bs, M::add(M::div(dxp_txz, k.dx), M::div(dzp_tzz, k.dz)))));
   } else {
-    const double bs = b * k.sdt;
-    vx = tp * (vx + bs * (dxm_txx * k.rdx + dzm_txz * k.rdz));
-    vz = tp * (vz + bs * (dxp_txz * k.rdx + dzp_tzz * k.rdz));
+    const double bs = __dmul_rn(b, k.sdt);
+    vx = __dmul_rn(tp, __fma_rn(bs, __fma_rn(dxm_txx, k.rdx, __dmul_rn(dzm_txz, k.rdz)), vx));
+    vz = __dmul_rn(tp, __fma_rn(bs, __fma_rn(dxp_txz, k.rdx, __dmul_rn(dzp_tzz, k.rdz)), vz));
   }
 }
 

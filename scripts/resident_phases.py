@@ -10,8 +10,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import psvwave_b200  # noqa: E402
 from helpers import C1_INI  # noqa: E402
 
-PHASES = ["halo: poll + load the neighbours' velocity packets", "snapshot / correlation / receivers",
-          "stress update + barrier", "velocity update", "injection + barrier", "publish own velocity rows", "-", "-"]
+PHASES = ["halo: poll + load the neighbours' velocity packets, barrier", "stress rows + barrier",
+          "velocity rows + injections + packets out + barrier", "snapshot / correlation / receivers of the next step",
+          "-", "-", "-", "-"]
 for opts in [dict(a.split("=") for a in arg.split(",") if a) for arg in (sys.argv[1:] or [""])]:
     m = psvwave_b200.fdModel(C1_INI)
     m._set_option("resident", 1)
