@@ -261,6 +261,13 @@ int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields);
 /* Enqueue up to n time steps on the model's stream (no wait); *done = steps enqueued, 0 at the end. */
 int psv_march_steps(psv_handle h, int n, int *done);
 int psv_march_end(psv_handle h);
+/* All slabs of one grid inside ONE process -- one per GPU of the box (create each with psv_set_default_device(d)
+ * first), or several on one GPU -- march through forward_simulate (adjoint = 0) or adjoint_simulate of shot i_shot
+ * together.  Every halo_rows/4 steps each slab pulls the edge rows its neighbours own straight out of their state
+ * arrays into its own halo rows: peer-to-peer loads over NVLink by one copy kernel per slab, ordered between the
+ * slabs' streams by CUDA events; no staging buffers, no NCCL, no host synchronisation inside the march.  `slabs`
+ * holds ALL slabs in slab order.  Results are those of psv_march_begin / steps / pack-exchange-unpack / end. */
+int psv_march_slabs(const psv_handle *slabs, int n, int i_shot, int adjoint, int store_fields);
 /* Stage the owned edge rows of vx vz txx tzz txz into the send buffers / the received rows into
  * the halo (stream-ordered kernels).  Buffers: [5 fields][halo_rows * pitch] doubles per side,
  * `count` doubles each; a side without neighbour has NULL pointers. */

@@ -609,6 +609,17 @@ int psv_march_steps(psv_handle h, int n, int *done) {
 int psv_march_end(psv_handle h) {
   return guarded([&] { model(h).march_end(); });
 }
+int psv_march_slabs(const psv_handle *slabs, int n, int i_shot, int adjoint, int store_fields) {
+  return guarded([&] {
+    if (!slabs || n < 1) throw psv::invalid_argument("psv_march_slabs needs the slabs of one grid.");
+    std::vector<psv::Model *> v(n);
+    for (int i = 0; i < n; ++i) {
+      single_device_only(slabs[i], "The domain split (psv_march_slabs)");
+      v[i] = &model(slabs[i]);
+    }
+    psv::Model::march_slabs(v.data(), n, i_shot, adjoint != 0, store_fields != 0);
+  });
+}
 int psv_halo_pack(psv_handle h) {
   return guarded([&] { model(h).halo_pack(); });
 }

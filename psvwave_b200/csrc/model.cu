@@ -108,6 +108,8 @@ Model::~Model() {
   for (auto &g : graphs_)
     if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
   for (cudaEvent_t e : prof_events_) cudaEventDestroy(e);
+  for (cudaEvent_t e : {slab_done_[0], slab_done_[1], slab_pulled_[0], slab_pulled_[1]})
+    if (e) cudaEventDestroy(e);
   if (ev_begin_) cudaEventDestroy(ev_begin_);
   if (ev_end_) cudaEventDestroy(ev_end_);
   if (ev_t0_) cudaEventDestroy(ev_t0_);
@@ -1587,6 +1589,135 @@ void Model::halo_unpack() {
   halo_copy_kernel<false><<<dim3(64, 10), 256, 0, stream_>>>(a);
   PSV_CUDA(cudaGetLastError());
   ++stat_launches_;
+}
+
+// ---- the slabs of one process exchange halos peer to peer ----
+namespace {
+struct PullArgs {
+  double *dst;         // my vx (current buffer); field k at + k * field_stride
+  size_t dst_stride;
+  const double *src[2];  // the neighbour's vx (current buffer) per side, or null
+  size_t src_stride[2];
+  size_t dst_off[2], src_off[2];  // first element of the H rows inside a field
+  size_t chunk;                   // H * ld
+};
+__global__ void halo_pull_kernel(const PullArgs a) {
+  const int side = blockIdx.y / 5, field = blockIdx.y % 5;
+  if (!a.src[side]) return;
+  const double2 *src = reinterpret_cast<const double2 *>(a.src[side] + field * a.src_stride[side] + a.src_off[side]);
+  double2 *dst = reinterpret_cast<double2 *>(a.dst + field * a.dst_stride + a.dst_off[side]);
+  const size_t n2 = a.chunk >> 1;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];  // loads cross NVLink when the neighbour lives on another GPU (peer access)
+}
+}  // namespace
+
+void Model::pull_halos(const Model *lower, const Model *upper) {
+  bind();
+  const int H = std::max(halo_lo_, halo_hi_);
+  if (H == 0) return;
+  const Model *nb[2] = {halo_lo_ ? lower : nullptr, halo_hi_ ? upper : nullptr};
+  bool direct = true;
+  for (const Model *o : nb)
+    if (o && o->device_ != device_) {
+      int can = 0;
+      PSV_CUDA(cudaDeviceCanAccessPeer(&can, device_, o->device_));
+      if (!can) {
+        direct = false;
+        continue;
+      }
+      if (!slab_peer_checked_) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(o->device_, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) PSV_CUDA(e);
+        cudaGetLastError();
+      }
+    }
+  slab_peer_checked_ = true;
+  // my rows [0, H) <- the lower neighbour's last H owned rows; my rows [nx-H, nx) <- the upper one's first H owned rows
+  const size_t chunk = (size_t)H * ld_;
+  const size_t dst_off[2] = {0, (size_t)(cfg_.nx - H) * ld_};
+  size_t src_off[2] = {0, 0};
+  if (nb[0]) src_off[0] = (size_t)(nb[0]->cfg_.nx - nb[0]->halo_hi_ - H) * ld_;
+  if (nb[1]) src_off[1] = (size_t)nb[1]->halo_lo_ * ld_;
+  if (direct) {
+    PullArgs a{F(0), field_stride_, {nb[0] ? nb[0]->F(0) : nullptr, nb[1] ? nb[1]->F(0) : nullptr},
+               {nb[0] ? nb[0]->field_stride_ : 0, nb[1] ? nb[1]->field_stride_ : 0},
+               {dst_off[0], dst_off[1]}, {src_off[0], src_off[1]}, chunk};
+    halo_pull_kernel<<<dim3(32, 10), 256, 0, stream_>>>(a);
+    PSV_CUDA(cudaGetLastError());
+    ++stat_launches_;
+    return;
+  }
+  for (int side = 0; side < 2; ++side)  // no peer mapping between the two GPUs: the copy engine routes it
+    if (nb[side])
+      for (int k = 0; k < 5; ++k)
+        PSV_CUDA(cudaMemcpyPeerAsync(F(k) + dst_off[side], device_, nb[side]->F(k) + src_off[side], nb[side]->device_,
+                                     chunk * sizeof(double), stream_));
+}
+
+void Model::march_slabs(Model *const *slabs, int n, int i_shot, bool adjoint, bool store_fields) {
+  if (n < 1 || !slabs) throw invalid_argument("psv_march_slabs needs the slabs of one grid.");
+  const int H = n > 1 ? std::max(slabs[0]->halo_lo_, slabs[0]->halo_hi_) : 4;
+  int next_row = 0;
+  for (int i = 0; i < n; ++i) {
+    Model *m = slabs[i];
+    if (!m->slab_) throw state_error("psv_march_slabs: not a slab of a split grid.");
+    const bool lo = i > 0, hi = i < n - 1;
+    if ((m->halo_lo_ > 0) != lo || (m->halo_hi_ > 0) != hi || (lo && m->halo_lo_ != H) || (hi && m->halo_hi_ != H) ||
+        m->nx_global_ != slabs[0]->nx_global_ || m->ld_ != slabs[0]->ld_ || m->x_off_ + m->halo_lo_ != next_row)
+      throw invalid_argument("psv_march_slabs: pass ALL slabs of one grid, in slab order, with one halo width.");
+    next_row = m->x_off_ + m->cfg_.nx - m->halo_hi_;
+    for (int p = 0; p < 2; ++p) {
+      m->bind();
+      if (!m->slab_done_[p]) PSV_CUDA(cudaEventCreateWithFlags(&m->slab_done_[p], cudaEventDisableTiming));
+      if (!m->slab_pulled_[p]) PSV_CUDA(cudaEventCreateWithFlags(&m->slab_pulled_[p], cudaEventDisableTiming));
+    }
+  }
+  if (next_row != slabs[0]->nx_global_) throw invalid_argument("psv_march_slabs: the slabs do not cover the grid.");
+  int begun = 0;
+  try {
+    for (; begun < n; ++begun) slabs[begun]->march_begin(i_shot, adjoint, store_fields);
+    const int k = H / 4;  // one step consumes 4 halo rows
+    int remaining = slabs[0]->cfg_.nt;
+    for (int round = 0; remaining > 0; ++round) {
+      const int steps = std::min(k, remaining), p = round & 1;
+      for (int i = 0; i < n; ++i) {
+        Model *m = slabs[i];
+        m->bind();
+        // The neighbours' pulls of the last exchange read my edge rows in the buffer my SECOND step of this round
+        // overwrites (ping-pong state): the first step runs while their "pulled" events travel.  (A one-step round
+        // needs no wait at all: my next "done" wait already orders me behind their pulls.)
+        int done = m->march_steps(1);
+        if (round > 0 && steps >= 2) {
+          if (i > 0) PSV_CUDA(cudaStreamWaitEvent(m->stream_, slabs[i - 1]->slab_pulled_[p ^ 1], 0));
+          if (i < n - 1) PSV_CUDA(cudaStreamWaitEvent(m->stream_, slabs[i + 1]->slab_pulled_[p ^ 1], 0));
+        }
+        if (steps >= 2) done += m->march_steps(steps - 1);
+        if (done != steps) throw state_error("psv_march_slabs: the slabs march out of step.");
+        PSV_CUDA(cudaEventRecord(m->slab_done_[p], m->stream_));
+      }
+      remaining -= steps;
+      if (remaining <= 0 || n == 1) continue;
+      for (int i = 0; i < n; ++i) {
+        Model *m = slabs[i];
+        m->bind();
+        if (i > 0) PSV_CUDA(cudaStreamWaitEvent(m->stream_, slabs[i - 1]->slab_done_[p], 0));
+        if (i < n - 1) PSV_CUDA(cudaStreamWaitEvent(m->stream_, slabs[i + 1]->slab_done_[p], 0));
+        m->pull_halos(i > 0 ? slabs[i - 1] : nullptr, i < n - 1 ? slabs[i + 1] : nullptr);
+        PSV_CUDA(cudaEventRecord(m->slab_pulled_[p], m->stream_));
+      }
+    }
+  } catch (...) {
+    for (int i = 0; i < begun; ++i) {  // leave no slab with a march in progress
+      try {
+        slabs[i]->march_.active = false;
+        slabs[i]->synchronize();
+      } catch (...) {
+      }
+    }
+    throw;
+  }
+  for (int i = 0; i < n; ++i) slabs[i]->march_end();
 }
 
 void Model::halo_buffers(void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) const {

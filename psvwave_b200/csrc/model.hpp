@@ -115,6 +115,10 @@ class Model {
   void halo_unpack();  // receive buffers -> halo rows of the 5 fields
   void halo_buffers(void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) const;
   void slab_info(long long out[7]) const;
+  // All slabs of one grid inside ONE process (one per GPU, or several on one): the whole march of shot i_shot with
+  // peer-to-peer halo pulls between the slabs' state arrays, ordered by CUDA events (no staging, no NCCL, no host
+  // synchronisation inside the march).  `slabs` in slab order, all of them.
+  static void march_slabs(Model *const *slabs, int n, int i_shot, bool adjoint, bool store_fields);
   cudaStream_t stream() const { return stream_; }
   static void forward_batch(Model *const *models, int n, int i_shot, bool store_fields);
   static void adjoint_batch(Model *const *models, int n, int i_shot);
@@ -221,6 +225,9 @@ class Model {
     bool active = false, adjoint = false, store = false;
     int i_shot = 0, it = 0;
   } march_;
+  void pull_halos(const Model *lower, const Model *upper);  // neighbours' owned edge rows -> my halo rows
+  cudaEvent_t slab_done_[2] = {nullptr, nullptr}, slab_pulled_[2] = {nullptr, nullptr};  // by exchange parity
+  bool slab_peer_checked_ = false;
   int device_ = 0;
   cudaStream_t stream_ = nullptr;
   cudaEvent_t ev_begin_ = nullptr, ev_end_ = nullptr, ev_t0_ = nullptr, ev_t1_ = nullptr;

@@ -380,6 +380,15 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
     for (int i = 0; i < PSV_ARRAY_COUNT_; ++i) d[names[i]] = i;
     return d;
   });
+  // additive: all slabs of a split grid inside one process, peer-to-peer halos (psv_march_slabs)
+  m.def(
+      "march_slabs",
+      [](const std::vector<FdModel *> &slabs, int i_shot, bool adjoint, bool store_fields) {
+        std::vector<psv_handle> h;
+        for (FdModel *s : slabs) h.push_back(s->handle());
+        check(psv_march_slabs(h.data(), (int)h.size(), i_shot, adjoint, store_fields));
+      },
+      py::arg("slabs"), py::arg("i_shot"), py::arg("adjoint"), py::arg("store_fields"));
   // additive: Monte-Carlo ensembles, one launch per time step for all models (psv_forward_batch)
   m.def(
       "forward_batch",

@@ -7,11 +7,16 @@ over its own rows plus ``halo_rows`` rows of each neighbour (``psv_create_slab_f
 One fused time step consumes 4 halo rows, so ``halo_rows = 4 * k`` lets k steps run between two
 exchanges (default k = 4: 16 rows, ~3 % redundant work on 1000-row slabs, 4x fewer exchanges).
 
-Two transports, one code path:
+Three transports, same results:
+  * ONE process drives all slabs, one per GPU of the box (``devices=[0, 1, ...]``) or several on one
+    GPU: the whole march is native (``psv_march_slabs``) -- every slab pulls its neighbours' edge rows
+    straight out of their state arrays over NVLink (peer-to-peer loads by one copy kernel), ordered by
+    CUDA events between the slabs' streams; no staging, no NCCL, no PyTorch, no host synchronisation
+    inside the march.  This is the default whenever the slabs live in one process;
   * one process per GPU (torchrun): each rank holds ONE slab; halos travel as NCCL point-to-point
     sends over NVLink (``torch.distributed.batch_isend_irecv`` on views of the staging buffers);
-  * ``n_slabs`` slabs inside one process on one GPU (tests, debugging): halos travel as device
-    copies.  Same staging kernels, same order, same results.
+  * ``native=False``: slabs inside one process with staged device copies (the test doubles of the CPU
+    tests use this path).
 
 What is exchanged per side and exchange: 5 fields x halo_rows x pitch doubles, one contiguous
 message.  Snapshots, sensitivity kernels and receiver samples are pointwise and stay local;
@@ -32,7 +37,8 @@ class SlabDomain:
 
     def __init__(self, ini: str, n_slabs: Optional[int] = None, halo_steps: int = 4, group=None,
                  rank: Optional[int] = None, world_size: Optional[int] = None, options: Optional[dict] = None,
-                 slab_factory=None, async_exchange: bool = True):
+                 slab_factory=None, async_exchange: bool = True, devices: Optional[List[int]] = None,
+                 native: bool = True):
         if rank is None or world_size is None:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
@@ -43,9 +49,12 @@ class SlabDomain:
         self.halo_rows = 4 * int(halo_steps)
         self.async_exchange = bool(async_exchange)
         self._views_cache = None
+        self._native = False
+        set_device = None
         if slab_factory is None:
-            from . import fdModel
+            from . import fdModel, set_default_device as set_device
             slab_factory = fdModel._slab
+            self._native = bool(native)
         if self.world_size > 1:
             if n_slabs not in (None, self.world_size):
                 raise ValueError("one slab per rank: n_slabs must equal the world size")
@@ -54,7 +63,16 @@ class SlabDomain:
             self.n_slabs = int(n_slabs or 1)
             mine = list(range(self.n_slabs))
         self.slab_ranks = mine
-        self.slabs = [slab_factory(ini, r, self.n_slabs, self.halo_rows) for r in mine]
+        if devices and self.world_size > 1:
+            raise ValueError("devices= places the slabs of ONE process; with one process per GPU each rank uses its own")
+        self.devices = [int(d) for d in devices] if devices else None
+        self.slabs = []
+        for r in mine:
+            if self.devices and set_device is not None:
+                set_device(self.devices[r % len(self.devices)])  # slab r lives on that GPU
+            self.slabs.append(slab_factory(ini, r, self.n_slabs, self.halo_rows))
+        if self.devices and set_device is not None:
+            set_device(self.devices[0])
         for m in self.slabs:
             for k, v in (options or {}).items():
                 m._set_option(k, int(v))
@@ -136,9 +154,16 @@ class SlabDomain:
         self._march(i_shot, True, False)
 
     def _march(self, i_shot: int, adjoint: bool, store: bool) -> None:
-        for m in self.slabs:
-            m._march_begin(i_shot, adjoint, store)
+        self.exchanges = (self.nt - 1) // max(self.halo_rows // 4, 1)
+        if self._native and self.world_size == 1:
+            from . import march_slabs
+            march_slabs(self.slabs, i_shot, adjoint, store)  # peer-to-peer halos, all inside the library
+            return
+        begun = []
         try:
+            for m in self.slabs:
+                m._march_begin(i_shot, adjoint, store)
+                begun.append(m)
             k = self.halo_rows // 4
             remaining = self.nt
             while remaining > 0:
@@ -150,9 +175,8 @@ class SlabDomain:
                 if remaining > 0:
                     self.exchange_halos()
         finally:
-            for m in self.slabs:
+            for m in begun:  # only what was begun (a slab whose begin failed holds no march)
                 m._march_end()
-        self.exchanges = (self.nt - 1) // max(self.halo_rows // 4, 1)
 
     def _views(self, m):
         """(send_lo, send_hi, recv_lo, recv_hi) as torch tensors over the staging buffers."""

@@ -1,8 +1,11 @@
 """Domain split (BASELINE.json configs[4], SURVEY 8e "large single grids"): the grid cut into
-x-slabs with halo exchange must reproduce the whole-grid run.  Here the slabs live in one process
-on one GPU (halos travel as device copies through the same staging buffers and kernels the
-NCCL transport uses), so the bar is the strictest one: with "exact" arithmetic every array is
-BIT-IDENTICAL to the whole-grid CUDA run and to the CPU oracle; default arithmetic <= 1e-10.
+x-slabs with halo exchange must reproduce the whole-grid run.  Here the slabs live in one process:
+"native" = the whole march inside the library (psv_march_slabs: peer-to-peer pulls between the
+slabs' state arrays, CUDA events between their streams), on one GPU or one slab per GPU when the
+box has several; "staged" = pack kernel -> device copy -> unpack kernel, the buffers and kernels
+the NCCL transport of the one-process-per-GPU layout uses.  The bar is the strictest one: with
+"exact" arithmetic every array is BIT-IDENTICAL to the whole-grid CUDA run and to the CPU oracle;
+default arithmetic <= 1e-10.
 """
 import numpy as np
 import pytest
@@ -66,11 +69,25 @@ def case(tmp_path_factory):
     return dict(ini=ini, medium=medium, obs=obs, oracle=ref, shape=(nx, nz))
 
 
+def gpus():
+    import psvwave_b200
+    return psvwave_b200.device_count()
+
+
+@pytest.mark.parametrize("transport", ["native", "staged", "native-multi-gpu"])
 @pytest.mark.parametrize("n_slabs,halo_steps,variant", [(2, 1, 3), (2, 4, 3), (3, 2, 3), (4, 4, 2), (3, 1, 2), (1, 4, 3)])
-def test_split_grid_is_bit_identical_to_whole_grid_and_oracle(case, n_slabs, halo_steps, variant):
+def test_split_grid_is_bit_identical_to_whole_grid_and_oracle(case, n_slabs, halo_steps, variant, transport):
     import psvwave_b200
     opts = dict(variant=variant, exact=1)
-    d = psvwave_b200.SlabDomain(case["ini"], n_slabs=n_slabs, halo_steps=halo_steps, options=opts)
+    devices = None
+    if transport == "native-multi-gpu":
+        if gpus() < 2:
+            pytest.skip("needs 2 CUDA devices")
+        devices = list(range(min(gpus(), n_slabs)))  # more slabs than GPUs: dealt round-robin
+    d = psvwave_b200.SlabDomain(case["ini"], n_slabs=n_slabs, halo_steps=halo_steps, options=opts,
+                                native=transport != "staged", devices=devices)
+    if devices and n_slabs > 1:
+        assert [int(m.device) for m in d.slabs] == [devices[k % len(devices)] for k in range(n_slabs)]
     assert (d.nx, d.nz) == case["shape"]
     owned = [d.owned_rows(k)[0] for k in range(n_slabs)]
     assert owned[0][0] == 0 and owned[-1][1] == d.nx and all(a[1] == b[0] for a, b in zip(owned, owned[1:]))
