@@ -280,6 +280,82 @@ def run_reference_arm(args) -> None:
 
 
 # ---------------------------------------------------------------------------------------------
+# extras (reported next to the headline, never part of `value`): the other two multi-GPU layouts, driven by rank 0
+# alone from ONE process over all `n_gpus` devices while the other ranks wait on the host
+# ---------------------------------------------------------------------------------------------
+def extra_slab_split(n_gpus: int, nt: int = 200) -> dict:
+    """BASELINE.json configs[4]: ONE 8100 x 4100 grid cut into one x-slab per GPU (psv_march_slabs:
+    peer-to-peer halo pulls over NVLink), forward(store) + adjoint of one shot -- strong scaling over n_gpus."""
+    import psvwave_b200
+    cfg = workload_config(nt, 1, dict(nx_inner=8000, nz_inner=4000, np_boundary=50, nr=64, snapshot_interval=50))
+    cfg.update(n_sources=1, n_shots=1, ix_sources=[4000], iz_sources=[20], moment_angles=[90.0],
+               which_source_to_fire_in_which_shot=[[0]], snapshot_interval=50)
+    ini = os.path.join(tempfile.mkdtemp(prefix="psv_bench_slab_"), "c5.ini")
+    write_ini(ini, cfg)
+    d = psvwave_b200.SlabDomain(ini, n_slabs=n_gpus, halo_steps=4, devices=list(range(n_gpus)), rank=0, world_size=1)
+    for k, m in enumerate(d.slabs):  # homogeneous + one anomaly, slab by slab (no whole-grid host array)
+        a, b = d._rows(k)
+        x, z = np.arange(a, b)[:, None], np.arange(d.nz)[None, :]
+        blob = 1 + 0.1 * np.exp(-(((x - d.nx * 0.4) / 300.0) ** 2 + ((z - d.nz * 0.5) / 300.0) ** 2))
+        m.set_parameter_fields(2000.0 * blob, 800.0 * blob, 1500.0 * np.ones_like(blob))
+    zero = np.zeros((1, d.nr, d.nt))
+    d.set_observed_data(zero, zero)
+    d.reset_kernels()
+    d.forward_simulate(0, True)
+    d.calculate_l2_adjoint_sources()
+    d.adjoint_simulate(0)  # warm-up of both marches
+    best = None
+    for _ in range(2):
+        d.synchronize()
+        t0 = time.perf_counter()
+        d._march(0, False, True)
+        d._march(0, True, False)
+        d.synchronize()
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return {"workload": "C5-large-grid-forward+adjoint, one x-slab per GPU, peer-to-peer halos in one process",
+            "grid": [d.nx, d.nz], "nt": d.nt, "n_gpus": n_gpus, "halo_rows": d.halo_rows, "scaling": "strong",
+            "exchanges_per_march": d.exchanges if n_gpus > 1 else 0, "seconds": best,
+            "value": 2.0 * d.nx * d.nz * d.nt / best, "unit": "updates/s",
+            "timing": "host clock around both marches, every stream synchronised on both sides, best of 2"}
+
+
+def extra_one_object(n_gpus: int, nt: int = 1000) -> dict:
+    """psv_set_devices: ONE fdModel object over n_gpus devices, the reference's own user loop from a plain
+    single-process script (no torchrun, no PyTorch): one shot per GPU of the headline workload's geometry."""
+    import psvwave_b200
+    cfg = workload_config(nt, n_gpus)
+    ini = os.path.join(tempfile.mkdtemp(prefix="psv_bench_obj_"), "c2.ini")
+    write_ini(ini, cfg)
+    m = psvwave_b200.fdModel(ini)
+    m.set_devices(list(range(n_gpus)))
+    m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
+    zero = np.zeros((m.n_shots, m.nr, m.nt))
+    m.set_observed_data(zero, zero)
+    best = None
+    for _ in range(3):
+        m.synchronize()
+        t0 = time.perf_counter()
+        for s in range(m.n_shots):
+            m.forward_simulate(s)
+        m.calculate_l2_misfit()
+        m.calculate_l2_adjoint_sources()
+        m.reset_kernels()
+        for s in range(m.n_shots):
+            m.adjoint_simulate(s)
+        m.map_kernels_to_velocity()
+        g = m.get_gradient_vector()
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return {"workload": "C2 geometry, one shot per GPU, ONE object (psv_set_devices), the reference's call order",
+            "grid": [m.nx, m.nz], "nt": m.nt, "n_gpus": n_gpus, "n_shots": m.n_shots, "scaling": "weak", "seconds": best,
+            "value": 2.0 * m.n_shots * m.nx * m.nz * m.nt / best, "unit": "updates/s",
+            "allreduce_ms": m._get_stat("allreduce_ms") if n_gpus > 1 else 0.0,
+            "gradient_norm": float(np.linalg.norm(g)),
+            "timing": "host clock around the whole gradient incl. the gradient vector on the host, best of 3"}
+
+
+# ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
 def pinned_copy(a: np.ndarray):
@@ -302,8 +378,10 @@ def run_ours(args) -> None:
     if psvwave_b200.device_count() < 1:
         raise RuntimeError("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        host_group = dist.new_group(backend="gloo")  # host-side waits (no kernel spinning on the waiting GPUs)
     psvwave_b200.set_default_device(local)
 
     geom = dict(GEOM)
@@ -399,6 +477,20 @@ def run_ours(args) -> None:
         return float(t.item())
 
     dev_ms, wall_ms, e2e_ms = rank_max(dev_ms), rank_max(wall_ms), rank_max(e2e_ms)
+
+    # the other two multi-GPU layouts, from rank 0's process alone over all GPUs; the other ranks wait on the host
+    extra = {}
+    if not args.no_extra:
+        barrier()
+        if rank == 0:
+            for name, fn in (("slab_split", extra_slab_split), ("one_object_all_gpus", extra_one_object)):
+                try:
+                    extra[name] = fn(world)
+                except Exception as e:  # an extra never takes the headline down
+                    extra[name] = {"error": f"{type(e).__name__}: {e}"}
+            psvwave_b200.set_default_device(local)
+        if world > 1:
+            dist.barrier(group=host_group)
     updates_per_step = 2.0 * nx * nz * nt * world
     value = updates_per_step * args.steps / (dev_ms * 1e-3)
     e2e_value = updates_per_step * args.steps / (e2e_ms * 1e-3)
@@ -478,6 +570,8 @@ def run_ours(args) -> None:
         if cpu:
             line["cpu_baseline"] = cpu
             line["parity"] = parity
+        if extra:
+            line["extra"] = extra
         emit(line)
     if world > 1:
         dist.barrier()
@@ -502,6 +596,7 @@ def main() -> None:
     ap.add_argument("--nt", type=int, default=0, help="override the number of time steps (debug only)")
     ap.add_argument("--option", action="append", default=[], help="solver option name=value (debug only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the slab-split / one-object extras")
     args = ap.parse_args()
     # The solver and the reference print progress lines on stdout (src/fdModel.cpp:396,472);
     # keep stdout for the ONE JSON line: everything else goes to stderr.

@@ -300,6 +300,9 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
  *              (the step kernel is then shorter than the gap between two stream launches) and the same loop is
  *              run a second time; "graphs_cached" reads
  *              the number of graphs held.  "pdl" 1 = programmatic dependent launch of consecutive variant-3 steps
+ *   "tune"     launch geometry of the default step kernel chosen by MEASUREMENT at the first time loop of a model (a few
+ *              milliseconds of plain step launches over its own state arrays): -1 (default) = grids of >= 2^21 points,
+ *              0 = never (formula), 1 = always; "tuned_warps" / "tuned_strip" / "tune_ms" read the outcome (psv_get_stat)
  *   launch geometry (sweeps under profiles/): "strip" "block" (variants 0/1), "fused_strip"
  *              "fused_block" (2), "pipe_warps" "pipe_stages" "l2_mode" "l2_persist_mb" (3),
  *              "pair_warps" "pair_stages" "pair_strip" (4) */

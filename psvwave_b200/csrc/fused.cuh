@@ -180,15 +180,38 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
     rq_end = c.rec_row_start[xe];
   }
   constexpr int kNoRow = 0x7fffffff;
-  int rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
   int op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
-  // adjoint sources of the next receiver, fetched when the cursor moves (rows ahead of their use)
-  double nax = 0.0, naz = 0.0;
-  if (c.point_mode == POINT_ADJOINT && rq < rq_end) {
-    const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
-    nax = m.ax[t];
-    naz = m.az[t];
-  }
+  // The receivers of the strip ride in registers, one list entry per lane (row, column, trace and -- adjoint runs --
+  // this step's adjoint-source samples), fetched with all loads in flight at once; a receiver row then costs a few
+  // shuffles instead of three dependent global loads in EVERY warp of the launch (cold L1: ~0.5 us per receiver row,
+  // 5 % of a step with 300 receivers on the 3100 x 1320 grid).  The window moves on after 32 entries.
+  int win0 = rq, lx = kNoRow, lz = 0, lid = 0;
+  double lax = 0.0, laz = 0.0;
+  auto load_window = [&]() {
+    const int q = win0 + lane;
+    lx = kNoRow;
+    if (q < rq_end) {
+      lx = c.rec_x[q];
+      lz = c.rec_z[q];
+      lid = c.rec_id[q];
+      if (c.point_mode == POINT_ADJOINT) {
+        const size_t t = (size_t)lid * c.nt + rg.it;
+        lax = m.ax[t];
+        laz = m.az[t];
+      }
+    }
+  };
+  if (rq < rq_end) load_window();
+  int rec_next = __shfl_sync(0xffffffffu, lx, 0);
+  auto next_receiver = [&]() {  // advance the cursor; returns the row of the next receiver
+    ++rq;
+    if (rq >= rq_end) return kNoRow;
+    if (rq - win0 == 32) {
+      win0 = rq;
+      load_window();
+    }
+    return __shfl_sync(0xffffffffu, lx, rq - win0);
+  };
 
   // j = row whose stresses are updated in this iteration; velocities of row j-2 follow.
   int j = xs - 2;
@@ -251,9 +274,9 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       // receiver sampling from the old velocities (src/fdModel.cpp:576-596)
       if (c.point_mode == POINT_FORWARD && j == rec_next) {
         do {
-          const int z = c.rec_z[rq];
+          const int z = __shfl_sync(0xffffffffu, lz, rq - win0), id = __shfl_sync(0xffffffffu, lid, rq - win0);
           if (mine && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
+            const size_t t = (size_t)id * c.nt + rg.it;
             const double pvx = (z & 1) ? vx_0.y : vx_0.x, pvz = (z & 1) ? vz_0.y : vz_0.x;
             const double sx = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvx), c.dxdz) : (c.dt * pvx) * c.rdxdz;
             const double sz = M::kExact ? __ddiv_rn(__dmul_rn(c.dt, pvz), c.dxdz) : (c.dt * pvz) * c.rdxdz;
@@ -265,8 +288,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
               m.uz[t] = __dadd_rn(m.uz[t - 1], sz);
             }
           }
-          ++rq;
-          rec_next = rq < rq_end ? c.rec_x[rq] : kNoRow;
+          rec_next = next_receiver();
         } while (rec_next == j);
       }
     }
@@ -339,7 +361,9 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       if (x == op_next) {
         // The operations of this row are fetched by the lanes in parallel (lane l takes operation oq + l and its
         // source-time-function sample: two global round trips for the whole row instead of two per operation),
-        // then applied one after the other in list order by the lane that owns each target point.
+        // then applied one after the other in list order by the lane that owns each target point.  (Keeping the
+        // strip's operations in registers for the whole march, like the receivers, costs 8 registers and measured
+        // 2 % slower on the bench workload: sources touch 2 strips of 37, receivers every tenth row.)
         do {
           const int n = min(32, oq_end - oq);
           int oz = 0, ofs = 0;
@@ -379,7 +403,8 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
       // adjoint-source injection at the receivers (src/fdModel.cpp:951-958)
       if (c.point_mode == POINT_ADJOINT && x == rec_next) {
         do {
-          const int z = c.rec_z[rq];
+          const int z = __shfl_sync(0xffffffffu, lz, rq - win0);
+          const double nax = __shfl_sync(0xffffffffu, lax, rq - win0), naz = __shfl_sync(0xffffffffu, laz, rq - win0);
           if (own && (z >> 1) == kp) {
             const double bb = (z & 1) ? b.y : b.x;
             const double ax = M::kExact ? __ddiv_rn(__dmul_rn(__dmul_rn(c.dt, bb), nax), c.dxdz)
@@ -394,14 +419,7 @@ __device__ __forceinline__ void fused_march(const FusedCommon &c, const FusedMod
               vz.x = __dadd_rn(vz.x, az);
             }
           }
-          ++rq;
-          rec_next = kNoRow;
-          if (rq < rq_end) {
-            rec_next = c.rec_x[rq];
-            const size_t t = (size_t)c.rec_id[rq] * c.nt + rg.it;
-            nax = m.ax[t];
-            naz = m.az[t];
-          }
+          rec_next = next_receiver();
         } while (rec_next == x);
       }
       sink.velocity(x, rv, vx, vz, b);

@@ -384,6 +384,12 @@ Model::Model(const Model &o, int device, bool with_snapshots) : cfg_(o.cfg_), de
   pair_warps_ = o.pair_warps_;
   resident_ = o.resident_;
   resident_rows_ = o.resident_rows_;
+  tune_ = o.tune_;
+  if (device_ == o.device_) {  // a measurement of that GPU
+    tuned_batch_ = o.tuned_batch_;
+    tuned_warps_ = o.tuned_warps_;
+    tuned_strip_ = o.tuned_strip_;
+  }
   pair_stages_ = o.pair_stages_;
   pair_strip_ = o.pair_strip_;
   l2_persist_mb_ = o.l2_persist_mb_;
@@ -769,6 +775,7 @@ int Model::fused_auto_strip(int n_zwarps, int batch) {
 // configuration take 3 (84 pairs) instead of leaving 5 of 8 warps idle.
 int Model::pipe_warps() const {
   if (pipe_warps_ != 0) return pipe_warps_;
+  if (tuned_warps_ != 0) return tuned_warps_;
   int best = 8, cost = 1 << 30;
   for (int nw : {8, 4, 3}) {
     const int owned = nw * kFusedOwnedPairs;
@@ -797,6 +804,10 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
     *strip = fused_strip_;
     return;
   }
+  if (tuned_strip_ > 0 && tuned_batch_ == batch) {
+    *strip = tuned_strip_;
+    return;
+  }
   const int blocks_x = *tiles * batch;
   const int nx = cfg_.nx;
   for (int waves = 1;; ++waves) {
@@ -810,6 +821,96 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
       return;
     }
   }
+}
+
+// Launch geometry of the variant-3 step kernel by measurement.  On large grids the step is bandwidth-bound only when
+// the CTAs are balanced over the SMs: too many short strips re-read halo rows and refill their pipelines, too few long
+// ones leave SMs idle, and which consumer-warp count wins depends on how the row length tiles (on a 1044 x 4100 slab
+// the formula above gives 88.6 us per step, the best candidate 76.9; profiles/r2g_slab_shape.md).  So the first time
+// loop of a model (and of every ensemble size) spends a few milliseconds on plain step launches over its own state
+// arrays -- CTA counts that are small multiples of the SM count, for each compiled warp count -- and keeps the fastest.
+// Results do not depend on the geometry (same arithmetic per point), and the caller zeroes the state afterwards.
+// The candidates run with the point operations of the loop that follows (receiver samples / injections at time index
+// 0, which that loop writes again): the warp that carries them is the critical path of its CTA row.
+void Model::tune_pipe_geometry(int i_shot, int point_mode) {
+  const int batch = 1 + (int)batch_followers_.size();
+  if (variant_ != 3 || fp32_ || tune_ == 0 || pipe_warps_ != 0 || fused_strip_ != 0) return;
+  if (tune_ < 0 && (long long)cfg_.nx * cfg_.nz * batch < (1ll << 21)) return;  // small grids: latency rules, see above
+  if (tuned_strip_ > 0 && tuned_batch_ == batch) return;
+  bind();
+  const auto wall0 = std::chrono::steady_clock::now();
+  int sms = 0;
+  PSV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_));
+  fused_begin(i_shot, point_mode);
+  const int cur0 = cur_;
+  const long long launches0 = stat_launches_;
+  tuned_warps_ = tuned_strip_ = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  PSV_CUDA(cudaEventCreate(&e0));
+  PSV_CUDA(cudaEventCreate(&e1));
+  int best_w = 0, best_s = 0;
+  struct Candidate {
+    int warps, strip;
+    float ms;
+  };
+  std::vector<Candidate> cands;
+  try {
+    auto time_steps = [&](int nw, int strip, int steps) {
+      pipe_warps_ = nw;
+      fused_strip_ = strip;
+      pipe_resident_ = 0;
+      launch_fused(cfg_.dt, MODE_PLAIN, point_mode, i_shot, 0, 0);  // warm-up (attributes, caches)
+      PSV_CUDA(cudaEventRecord(e0, stream_));
+      for (int k = 0; k < steps; ++k) launch_fused(cfg_.dt, MODE_PLAIN, point_mode, i_shot, 0, 0);
+      PSV_CUDA(cudaEventRecord(e1, stream_));
+      PSV_CUDA(cudaEventSynchronize(e1));
+      float ms = 0;
+      PSV_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      return ms / steps;
+    };
+    for (int nw : kPipeWarpChoices) {
+      const int owned = nw * kFusedOwnedPairs, tiles = (ld_ / 2 + owned - 1) / owned;
+      if (pipe_smem_bytes(nw, pipe_stages_, false) > kMaxDynamicSmem) continue;
+      int last_strip = 0;
+      for (int f = 1; f <= 8; ++f) {  // about f CTAs per SM in total
+        const int n_strips = std::max(1, f * sms / (tiles * batch));  // at most f CTAs per SM: no ragged last wave
+        const int strip = (cfg_.nx + n_strips - 1) / n_strips;
+        if (strip == last_strip || strip < 16) continue;
+        last_strip = strip;
+        cands.push_back({nw, strip, 0.f});
+      }
+    }
+    if (cands.empty()) cands.push_back({8, std::max(cfg_.nx, 1), 0.f});
+    time_steps(cands[0].warps, cands[0].strip, 12);  // clocks up before anything is compared
+    for (Candidate &c : cands) c.ms = time_steps(c.warps, c.strip, 3);
+    std::sort(cands.begin(), cands.end(), [](const Candidate &x, const Candidate &y) { return x.ms < y.ms; });
+    float best_ms = 1e30f;
+    for (size_t i = 0; i < cands.size() && i < 4; ++i) {  // the leaders again, longer
+      const float ms = time_steps(cands[i].warps, cands[i].strip, 10);
+      if (ms < best_ms) {
+        best_ms = ms;
+        best_w = cands[i].warps;
+        best_s = cands[i].strip;
+      }
+    }
+  } catch (...) {
+    pipe_warps_ = fused_strip_ = 0;
+    pipe_resident_ = 0;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    throw;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  pipe_warps_ = fused_strip_ = 0;
+  pipe_resident_ = 0;
+  tuned_warps_ = best_w;
+  tuned_strip_ = best_s;
+  tuned_batch_ = batch;
+  cur_ = cur0;
+  stat_launches_ = launches0;
+  drop_graphs();
+  stat_tune_ms_ = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
 }
 
 // Depth of the input ring of variant 4: the option, or (0) as many stages as fit next to the exchange ring.
@@ -1128,7 +1229,7 @@ std::vector<unsigned long long> Model::graph_key(int direction, int i_shot, bool
   auto n = [](long long v) { return (unsigned long long)v; };
   const ShotPlan &plan = plans_[i_shot];
   return {n(direction > 0), n(i_shot), n(store), n(variant_), n(exact_), n(fp32_), n(fused_strip_), n(fused_block_),
-          n(pipe_stages_), n(pipe_warps_), n(pdl_), n(l2_mode_), n(pair_warps_),
+          n(pipe_stages_), n(pipe_warps_), n(tuned_warps_), n(tuned_strip_), n(pdl_), n(l2_mode_), n(pair_warps_),
           n(pair_stages()), n(pair_strip_), n((long long)batch_followers_.size()), p(fused_model_.as<char>()),
           p(fused_model32_.as<char>()), p(fields_.as<char>()), n((long long)fields_.bytes()), p(fields32_.as<char>()),
           n((long long)fields32_.bytes()), p(taper_table_.as<char>()), p(rec_row_start_.as<char>()),
@@ -1260,6 +1361,7 @@ void Model::forward_simulate(int i_shot, bool store_fields, bool verbose, bool o
     }
     return;
   }
+  if (!use_graph) tune_pipe_geometry(i_shot, POINT_FORWARD);
   if (use_graph) graph_capture_begin();
   try {
   zero_dynamic_fields();
@@ -1413,6 +1515,7 @@ void Model::adjoint_simulate(int i_shot, bool verbose) {
     }
     return;
   }
+  if (!use_graph) tune_pipe_geometry(i_shot, c.nr > 0 ? POINT_ADJOINT : POINT_NONE);
   if (use_graph) graph_capture_begin();
   try {
   zero_dynamic_fields();
@@ -1493,6 +1596,7 @@ void Model::march_begin(int i_shot, bool adjoint, bool store_fields) {
   if (!adjoint && store_fields) ensure_snapshots(i_shot);
   stat_launches_ = 0;
   stat_pair_launches_ = 0;
+  tune_pipe_geometry(i_shot, adjoint ? (cfg_.nr > 0 ? POINT_ADJOINT : POINT_NONE) : POINT_FORWARD);
   zero_dynamic_fields();
   PSV_CUDA(cudaEventRecord(ev_begin_, stream_));
   fused_begin(i_shot, adjoint ? POINT_ADJOINT : POINT_FORWARD);
@@ -2348,7 +2452,11 @@ void Model::load_vector(const std::string &path, bool verbose, double *out, size
 // options / statistics
 // ---------------------------------------------------------------------------------------------
 void Model::set_option(const std::string &name, long long v) {
-  if (name == "variant") {
+  tuned_warps_ = tuned_strip_ = tuned_batch_ = 0;  // measured for the options that were in force
+  pipe_resident_ = 0;
+  if (name == "tune") {
+    tune_ = (int)std::max(-1ll, std::min(1ll, v));
+  } else if (name == "variant") {
     if (v < 0 || v >= kVariantCount) throw invalid_argument("variant out of range");
     variant_ = (int)v;
   } else if (name == "exact") {
@@ -2438,6 +2546,7 @@ long long Model::get_option(const std::string &name) const {
   if (name == "pdl") return pdl_ ? 1 : 0;
   if (name == "resident") return resident_;
   if (name == "resident_rows") return resident_rows_;
+  if (name == "tune") return tune_;
   if (name == "graph") return graph_;
   if (name == "graphs_cached") return (long long)graphs_.size();
   if (name == "l2_persist_mb") return l2_persist_mb_;
@@ -2455,6 +2564,9 @@ double Model::get_stat(const std::string &name) const {
   if (name == "velocity_ms") return stat_velocity_ms_;
   if (name == "pair_launches") return (double)stat_pair_launches_;
   if (name == "resident_ctas") return (double)stat_resident_;
+  if (name == "tuned_warps") return tuned_warps_;
+  if (name == "tuned_strip") return tuned_strip_;
+  if (name == "tune_ms") return stat_tune_ms_;
   if (name.rfind("resident_phase_max", 0) == 0 && name.size() == 19 && name[18] >= '0' && name[18] <= '7')
     return stat_resident_phase_max_[name[18] - '0'];
   if (name.rfind("resident_phase", 0) == 0 && name.size() == 15 && name[14] >= '0' && name[14] <= '7')

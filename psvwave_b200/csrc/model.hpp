@@ -199,6 +199,7 @@ class Model {
   void adopt_batch_state(const Model &leader);
   int fused_auto_strip(int n_zwarps, int batch);
   int pipe_warps() const;
+  void tune_pipe_geometry(int i_shot, int point_mode);  // first use on a large grid: time a few (warps, strip) candidates, keep the best
   void pipe_geometry(int batch, int *tiles, int *strip, size_t *smem);
   void launch_fused(double sdt, int mode, int point_mode, int i_shot, int snap, int it, int pair_step = 0);
   void fill_fused_common(void *out, double sdt, int point_mode, int i_shot, int snap, int it);
@@ -280,6 +281,8 @@ class Model {
   int fused_strip_ = 0 /* 0 = whole waves */, fused_block_ = 128;
   int fused_resident_blocks_ = 0;
   int pipe_stages_ = 4, pipe_warps_ = 0 /* 0 = auto */, pipe_resident_ = 0;
+  int tune_ = -1 /* -1 = auto (large grids), 0 = off, 1 = on */, tuned_batch_ = 0, tuned_warps_ = 0, tuned_strip_ = 0;
+  double stat_tune_ms_ = 0;
   int l2_persist_mb_ = 0;  // persisting-L2 carve-out for the medium arrays the step kernel re-reads (0 = off)
   void apply_l2_window();
   bool pdl_ = false;  // programmatic dependent launch of consecutive variant-3 step kernels

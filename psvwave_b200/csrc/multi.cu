@@ -30,10 +30,16 @@ const Nccl &nccl() {
   static std::once_flag once;
   static std::string failure;
   std::call_once(once, [] {
-    void *lib = nullptr;
+    // 1. a libnccl.so.2 the process already holds (PyTorch's); 2. the one PSVWAVE_NCCL_LIBRARY names (the Python
+    // package points it at the NCCL wheel PyTorch would load later, so that both end up with the same, newest copy --
+    // an older system libnccl loaded first would leave PyTorch's import with missing symbols); 3. the system library.
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!lib)
+      if (const char *path = std::getenv("PSVWAVE_NCCL_LIBRARY"))
+        if (*path) lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
     for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
-      lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
       if (lib) break;
+      lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
     }
     if (!lib) {
       failure = std::string("NCCL is needed to sum the kernels of several GPUs and could not be loaded: ") + dlerror();

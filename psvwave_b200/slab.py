@@ -40,11 +40,12 @@ class SlabDomain:
                  slab_factory=None, async_exchange: bool = True, devices: Optional[List[int]] = None,
                  native: bool = True):
         if rank is None or world_size is None:
-            import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized():
+            import sys
+            dist = sys.modules.get("torch.distributed")  # an initialised process group implies the import
+            if dist is not None and dist.is_available() and dist.is_initialized():
                 rank, world_size = dist.get_rank(group), dist.get_world_size(group)
             else:
-                rank, world_size = 0, 1
+                rank, world_size = 0, 1  # all slabs in this process: PyTorch is not needed
         self.group, self.rank, self.world_size = group, int(rank), int(world_size)
         self.halo_rows = 4 * int(halo_steps)
         self.async_exchange = bool(async_exchange)
