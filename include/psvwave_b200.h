@@ -235,6 +235,22 @@ int psv_run_gradient(psv_handle h, int release_each_shot, double *misfit_out);
 int psv_descent_step(psv_handle h, double step_length);
 int psv_gradient_descent(psv_handle h, int iterations, double step_length, int release_each_shot,
                          double *misfits_out);
+/* The rest of the reference's outer loop on the device.  The reference's notebooks and docs
+ * (docs-source/source/typical-workflow.rst:16-72; Notebook 2 cells 15-17) hand get_model_vector / get_gradient_vector to
+ * SciPy: scipy.ndimage.gaussian_filter(panel.reshape(nz_free, nx_free), sigma) on the three thirds of the gradient vector,
+ * then scipy.optimize.minimize(method="L-BFGS-B", maxcor=10, maxiter=50, gtol=1e-6).
+ * psv_get_gradient_vector_smoothed: the gradient vector after exactly that filter (separable, mode "reflect", truncate 4.0,
+ * scipy's summation order), computed on the device; sigma = 0 is psv_get_gradient_vector.
+ * psv_lbfgs: L-BFGS with `history` (s, y) pairs on the device-resident model vector -- two-loop recursion, initial scaling
+ * s.y / y.y, first step 1/|g| like L-BFGS-B, unit step afterwards with backtracking on the sufficient-decrease
+ * condition -- every evaluation being psv_run_gradient (+ the smoothing when smoothing_sigma > 0).  Starts from the
+ * object's current medium, stops after max_iterations or when max|g| <= gtol, leaves the final medium in the object.
+ * misfits_out[0 .. *iterations_done] (capacity max_iterations + 1, may be NULL) receives the misfit before the first and
+ * after every iteration.  Not bit-comparable with SciPy's L-BFGS-B (another line search); the tests compare the misfit
+ * reached on the notebook-2 problem. */
+int psv_get_gradient_vector_smoothed(psv_handle h, double sigma, double *out, size_t n);
+int psv_lbfgs(psv_handle h, int max_iterations, int history, double gtol, double smoothing_sigma,
+              int release_each_shot, double *misfits_out, int *iterations_done, int *evaluations_done);
 /* Monte-Carlo ensembles (SURVEY 8e "replicas only"; the reference's route is n independent copies of
  * the object, src/fdModel.cpp:64-97, each simulated on its own).  The n models must describe one
  * experiment on one device (same grid, time axis, boundary, sources, receivers, snapshot interval);

@@ -30,7 +30,7 @@ NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 HOST_CXX = "/usr/bin/g++"  # the image's $CXX wrapper (/opt/gcc) lacks a few spec files
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
-LIB_SOURCES = ["capi.cu", "model.cu", "multi.cu", "config.cpp", "launch_step.cu", "launch_pipe.cu", "launch_pair.cu",
+LIB_SOURCES = ["capi.cu", "model.cu", "multi.cu", "optim.cu", "config.cpp", "launch_step.cu", "launch_pipe.cu", "launch_pair.cu",
                "launch_resident.cu"]
 
 

@@ -555,6 +555,26 @@ int psv_gradient_descent(psv_handle h, int iterations, double step_length, int r
   });
 }
 
+int psv_get_gradient_vector_smoothed(psv_handle h, double sigma, double *out, size_t n) {
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->get_gradient_vector_smoothed(out, n, sigma);
+    else model(h).get_gradient_vector_smoothed(out, n, sigma);
+  });
+}
+int psv_lbfgs(psv_handle h, int max_iterations, int history, double gtol, double smoothing_sigma,
+              int release_each_shot, double *misfits_out, int *iterations_done, int *evaluations_done) {
+  return guarded([&] {
+    psv::LbfgsOptions opt;
+    opt.max_iterations = max_iterations;
+    opt.history = history;
+    opt.gtol = gtol;
+    const psv::LbfgsResult r = group(h) ? h->g->lbfgs(opt, smoothing_sigma, release_each_shot != 0, misfits_out)
+                                        : model(h).lbfgs(opt, smoothing_sigma, release_each_shot != 0, misfits_out);
+    if (iterations_done) *iterations_done = r.iterations;
+    if (evaluations_done) *evaluations_done = r.evaluations;
+  });
+}
+
 namespace {
 std::vector<psv::Model *> batch_models(const psv_handle *handles, int n) {
   if (!handles || n < 1) throw psv::invalid_argument("Batched simulate needs at least one model.");

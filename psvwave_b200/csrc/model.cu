@@ -2006,6 +2006,71 @@ void Model::gradient_descent(int iterations, double step, bool release_each_shot
   }
 }
 
+// ---- device-side vectors, smoothing, L-BFGS ----
+void Model::vector_from_fields(double *dev_m) {
+  bind();
+  if (slab_) throw state_error("Model vectors span the whole grid: not available on a slab.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  vector_kernel<VEC_MEAN><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(), dev_m);
+  PSV_CUDA(cudaGetLastError());
+}
+
+void Model::fields_from_vector(const double *dev_m) {
+  bind();
+  if (slab_) throw state_error("Model vectors span the whole grid: not available on a slab.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  vector_kernel<VEC_FILL><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_.data(), vs_.data(), rho_.data(),
+                                                                       const_cast<double *>(dev_m));
+  PSV_CUDA(cudaGetLastError());
+  update_from_velocity();  // src/fdModel.cpp:1456
+}
+
+void Model::gradient_to_vector(double *dev_g, double sigma) {
+  bind();
+  if (slab_) throw state_error("Gradient vectors span the whole grid: not available on a slab.");
+  const VectorArgs a = vector_args(cfg_, ld_);
+  vector_kernel<VEC_SUM><<<blocks_for(a.per, 128), 128, 0, stream_>>>(a, vp_kernel_.data(), vs_kernel_.data(),
+                                                                      density_v_kernel_.data(), dev_g);
+  PSV_CUDA(cudaGetLastError());
+  if (sigma > 0.0) {
+    // the reference's _fwi class reshapes every third of the vector to (nz_free, nx_free) -- entries are x fastest
+    // (src/fdModel.cpp:1501-1509) -- and filters it (docs-source/source/typical-workflow.rst:61-69)
+    const size_t n = (size_t)cfg_.free_parameters;
+    if (smooth_tmp_.bytes() < n * sizeof(double)) smooth_tmp_.allocate(n * sizeof(double));
+    gaussian_smooth_panels(dev_g, smooth_tmp_.as<>(), 3, a.nbz, a.nbx, sigma, stream_);
+  }
+}
+
+void Model::get_gradient_vector_smoothed(double *out, size_t n, double sigma) {
+  bind();
+  if (n != (size_t)cfg_.free_parameters) throw invalid_argument("Gradient vector has the wrong length.");
+  if (sigma < 0.0) throw invalid_argument("Smoothing sigma must be >= 0.");
+  if (scratch_.bytes() < n * sizeof(double)) scratch_.allocate(n * sizeof(double));
+  gradient_to_vector(scratch_.as<>(), sigma);
+  PSV_CUDA(cudaMemcpyAsync(out, scratch_.as<>(), n * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+}
+
+LbfgsResult Model::lbfgs(const LbfgsOptions &opt, double sigma, bool release_each_shot, double *misfits) {
+  bind();
+  if (sigma < 0.0) throw invalid_argument("Smoothing sigma must be >= 0.");
+  const size_t n = (size_t)cfg_.free_parameters;
+  DeviceBuffer x(n * sizeof(double));
+  vector_from_fields(x.as<>());
+  const LbfgsResult r = lbfgs_minimize(
+      x.as<>(), n,
+      [&](const double *m, double *g) {
+        fields_from_vector(m);
+        const double f = run_gradient(release_each_shot);
+        gradient_to_vector(g, sigma);
+        return f;
+      },
+      opt, misfits, stream_);
+  fields_from_vector(x.as<>());  // the line search may have ended on a rejected trial point
+  misfit_ = r.misfit;
+  return r;
+}
+
 void Model::update_from_velocity() {
   bind();
   update_from_velocity_kernel<<<blocks_for(grid_elems_, 256), 256, 0, stream_>>>(

@@ -11,6 +11,7 @@
 
 #include "../../include/psvwave_b200.h"
 #include "config.hpp"
+#include "optim.hpp"
 
 namespace psv {
 
@@ -102,6 +103,14 @@ class Model {
   void descent_load();
   void descent_apply(double step);
   void gradient_descent(int iterations, double step, bool release_each_shot, double *misfits);
+  // Device-resident L-BFGS on the model vector (optim.hpp; the reference's notebooks use SciPy's L-BFGS-B on the
+  // host): every evaluation is run_gradient; sigma > 0 smooths the gradient panels like the reference's _fwi class.
+  LbfgsResult lbfgs(const LbfgsOptions &opt, double sigma, bool release_each_shot, double *misfits);
+  void get_gradient_vector_smoothed(double *out, size_t n, double sigma);
+  // device-side halves of get_model_vector / set_model_vector / get_gradient_vector (vectors of free_parameters)
+  void vector_from_fields(double *dev_m);
+  void fields_from_vector(const double *dev_m);
+  void gradient_to_vector(double *dev_g, double sigma);
   // Monte-Carlo ensembles (SURVEY 8e "replicas only", config C4): n models that share one
   // experiment (grid, time axis, sources, receivers) advance together, ONE launch per time step
   // for the whole ensemble (blockIdx.z = model).  Each model keeps its own medium, fields,
@@ -268,6 +277,7 @@ class Model {
   std::vector<ShotPlan> plans_;
   std::vector<DeviceBuffer> snapshots_;  // per shot: [5][n_snap_alloc][nx][ld]
   std::vector<DeviceBuffer> snapshot_pool_;  // released buffers, reused by ensure_snapshots
+  DeviceBuffer smooth_tmp_;              // second buffer of the separable Gaussian smoothing
   DeviceBuffer descent_vec_;             // [model vector | gradient vector] of the device-resident descent
   DeviceBuffer scratch_;                 // reduction partials / vectors
 

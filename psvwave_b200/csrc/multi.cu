@@ -391,6 +391,34 @@ void DeviceGroup::gradient_descent(int iterations, double step, bool release_eac
   }
 }
 
+LbfgsResult DeviceGroup::lbfgs(const LbfgsOptions &opt, double sigma, bool release_each_shot, double *misfits) {
+  if (sigma < 0.0) throw invalid_argument("Smoothing sigma must be >= 0.");
+  reduce_kernels();
+  const size_t n = (size_t)primary_->config().free_parameters;
+  PSV_CUDA(cudaSetDevice(devices_[0]));
+  DeviceBuffer x(n * sizeof(double));
+  primary_->vector_from_fields(x.as<>());
+  const LbfgsResult r = lbfgs_minimize(
+      x.as<>(), n,
+      [&](const double *m, double *g) {
+        primary_->fields_from_vector(m);
+        broadcast_medium();
+        const double f = run_gradient(release_each_shot);  // all GPUs, one all-reduce
+        primary_->gradient_to_vector(g, sigma);
+        return f;
+      },
+      opt, misfits, primary_->stream());
+  primary_->fields_from_vector(x.as<>());
+  broadcast_medium();
+  primary_->set_misfit(r.misfit);
+  return r;
+}
+
+void DeviceGroup::get_gradient_vector_smoothed(double *out, size_t n, double sigma) {
+  drain();
+  primary_->get_gradient_vector_smoothed(out, n, sigma);
+}
+
 // ---------------------------------------------------------------------------------------------
 // vectors, arrays, files
 // ---------------------------------------------------------------------------------------------

@@ -62,6 +62,8 @@ class DeviceGroup {
   double run_gradient(bool release_each_shot);
   void descent_step(double step);
   void gradient_descent(int iterations, double step, bool release_each_shot, double *misfits);
+  LbfgsResult lbfgs(const LbfgsOptions &opt, double sigma, bool release_each_shot, double *misfits);
+  void get_gradient_vector_smoothed(double *out, size_t n, double sigma);
   void get_model_vector(double *out, size_t n);
   void set_model_vector(const double *in, size_t n);
   void get_gradient_vector(double *out, size_t n);

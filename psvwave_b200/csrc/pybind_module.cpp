@@ -262,6 +262,23 @@ class FdModel {
     check(psv_get_array(h_, (psv_array)which, out.mutable_data(), n));
     return out;
   }
+  py::array_t<double> smoothed_gradient(double sigma) const {
+    const py::ssize_t n = geti(PSV_INT_FREE_PARAMETERS);
+    py::array_t<double> out(n);
+    check(psv_get_gradient_vector_smoothed(h_, sigma, out.mutable_data(), (size_t)n));
+    return out;
+  }
+  py::tuple lbfgs(int iterations, int history, double gtol, double smoothing, bool release_each_shot) {
+    std::vector<double> misfits((size_t)std::max(iterations, 0) + 1, 0.0);
+    int done = 0, evals = 0;
+    {
+      py::gil_scoped_release release;
+      check(psv_lbfgs(h_, iterations, history, gtol, smoothing, release_each_shot, misfits.data(), &done, &evals));
+    }
+    py::array_t<double> out(done + 1);
+    std::copy(misfits.begin(), misfits.begin() + done + 1, out.mutable_data());
+    return py::make_tuple(out, evals);
+  }
   void set_option(const std::string &name, long long v) { check(psv_set_option(h_, name.c_str(), v)); }
   long long get_option(const std::string &name) const {
     long long v = 0;
@@ -471,6 +488,11 @@ PYBIND11_MODULE(__psvWave_cpp, m) {
       .def("descent_step", &FdModel::descent_step, py::arg("step_length"))
       .def("gradient_descent", &FdModel::gradient_descent, py::arg("iterations"), py::arg("step_length"),
            py::arg("release_each_shot") = true)
+      .def("get_smoothed_gradient_vector", &FdModel::smoothed_gradient, py::arg("sigma"),
+           "get_gradient_vector() after scipy.ndimage.gaussian_filter on its three (nz_free, nx_free) panels, on the device.")
+      .def("lbfgs", &FdModel::lbfgs, py::arg("iterations"), py::arg("history") = 10, py::arg("gtol") = 1e-6,
+           py::arg("smoothing") = 0.0, py::arg("release_each_shot") = true,
+           "Device-resident L-BFGS on the model vector; returns (misfits[0..iterations done], evaluations).")
       .def("write_receivers", &FdModel::write_receivers)
       .def("load_receivers", &FdModel::load_receivers, py::arg("verbose") = false)
       .def("write_sources", &FdModel::write_sources)
