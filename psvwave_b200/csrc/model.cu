@@ -505,6 +505,74 @@ void Model::zero_dynamic_fields() {
   if (fp32_) PSV_CUDA(cudaMemsetAsync(fields32_.as<char>(), 0, fields32_.bytes(), stream_));
   PSV_CUDA(cudaMemsetAsync(fields_.as<char>(), 0, fields_.bytes(), stream_));
   cur_ = 0;
+  if (poison_) poison_arrays(/*state_only=*/true);
+}
+
+// ---- debug: NaN canaries in everything the kernels may touch outside the grid proper ----
+namespace {
+constexpr unsigned long long kCanary = 0x7ff8dead0000beefull;  // a quiet NaN with a recognisable payload
+// One padded grid array [guard | nx rows of ld | guard]: canaries into both guards and the pad columns nz..ld-1.
+__global__ void poison_kernel(double *base, size_t guard, int nx, int ld, int nz) {
+  const size_t total = 2 * guard + (size_t)nx * ld;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    bool hit = i < guard || i >= guard + (size_t)nx * ld;
+    if (!hit) hit = (int)((i - guard) % ld) >= nz;
+    if (hit) reinterpret_cast<unsigned long long *>(base)[i] = kCanary;
+  }
+}
+__global__ void poison_range_kernel(double *p, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    reinterpret_cast<unsigned long long *>(p)[i] = kCanary;
+}
+// guards only (pads are legitimately rewritten with whatever sat there): anything but the canary is a stray write
+__global__ void count_guard_kernel(const double *base, size_t guard, size_t grid, unsigned long long *bad) {
+  unsigned long long mine = 0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * guard; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t at = i < guard ? i : grid + i;
+    if (reinterpret_cast<const unsigned long long *>(base)[at] != kCanary) ++mine;
+  }
+  if (mine) atomicAdd(bad, mine);
+}
+}  // namespace
+
+void Model::poison_arrays(bool state_only) {
+  bind();
+  const Config &c = cfg_;
+  for (int k = 0; k < 10; ++k)
+    poison_kernel<<<256, 256, 0, stream_>>>(fields_.as<double>() + (size_t)k * field_stride_, guard_, c.nx, ld_, c.nz);
+  if (!state_only) {
+    for (int k = 0; k < 3; ++k)
+      poison_kernel<<<256, 256, 0, stream_>>>(medium_.as<double>() + (size_t)k * field_stride_, guard_, c.nx, ld_, c.nz);
+    GridArray *grids[] = {&vp_, &vs_, &rho_, &vp_kernel_, &vs_kernel_, &density_v_kernel_};
+    for (GridArray *g : grids) poison_kernel<<<256, 256, 0, stream_>>>(g->buf.as<double>(), guard_, c.nx, ld_, c.nz);
+    // the slack around the Lame kernels and the snapshots that bulk copies of whole row segments run into
+    poison_range_kernel<<<8, 256, 0, stream_>>>(lame_kernels_.as<double>(), kBulkPad);
+    poison_range_kernel<<<8, 256, 0, stream_>>>(lame_kernels_.as<double>() + kBulkPad + 3 * grid_elems_, kBulkPad);
+    for (DeviceBuffer &s : snapshots_)
+      if (!s.empty() && !fp32_) {
+        poison_range_kernel<<<8, 256, 0, stream_>>>(s.as<double>(), kBulkPad);
+        poison_range_kernel<<<8, 256, 0, stream_>>>(s.as<double>() + kBulkPad + 5 * (size_t)n_snap_alloc_ * grid_elems_,
+                                                   kBulkPad);
+      }
+  }
+  PSV_CUDA(cudaGetLastError());
+}
+
+long long Model::count_guard_violations() {
+  bind();
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  DeviceBuffer bad(sizeof(unsigned long long));
+  std::vector<const double *> bases;
+  for (int k = 0; k < 10; ++k) bases.push_back(fields_.as<double>() + (size_t)k * field_stride_);
+  for (int k = 0; k < 3; ++k) bases.push_back(medium_.as<double>() + (size_t)k * field_stride_);
+  for (const GridArray *g : {&vp_, &vs_, &rho_, &vp_kernel_, &vs_kernel_, &density_v_kernel_})
+    bases.push_back(g->buf.as<double>());
+  for (const double *b : bases)
+    count_guard_kernel<<<64, 256, 0, stream_>>>(b, guard_, grid_elems_, bad.as<unsigned long long>());
+  PSV_CUDA(cudaGetLastError());
+  unsigned long long n = 0;
+  copy_sync(&n, bad.as<char>(), sizeof n, cudaMemcpyDeviceToHost);
+  return (long long)n;
 }
 
 void Model::ensure_snapshots(int i_shot) {
@@ -528,6 +596,11 @@ void Model::ensure_snapshots(int i_shot) {
          << e.what() << "]";
       throw length_error(os.str());
     }
+  }
+  if (poison_ && !fp32_) {  // the slack around the snapshots that bulk copies of whole row segments run into
+    poison_range_kernel<<<8, 256, 0, stream_>>>(s.as<double>(), kBulkPad);
+    poison_range_kernel<<<8, 256, 0, stream_>>>(s.as<double>() + kBulkPad + 5 * (size_t)n_snap_alloc_ * grid_elems_, kBulkPad);
+    PSV_CUDA(cudaGetLastError());
   }
 }
 
@@ -2519,7 +2592,13 @@ void Model::load_vector(const std::string &path, bool verbose, double *out, size
 void Model::set_option(const std::string &name, long long v) {
   tuned_warps_ = tuned_strip_ = tuned_batch_ = 0;  // measured for the options that were in force
   pipe_resident_ = 0;
-  if (name == "tune") {
+  if (name == "poison_guards") {
+    poison_ = v != 0;
+    if (poison_) {
+      poison_arrays(false);
+      PSV_CUDA(cudaStreamSynchronize(stream_));
+    }
+  } else if (name == "tune") {
     tune_ = (int)std::max(-1ll, std::min(1ll, v));
   } else if (name == "variant") {
     if (v < 0 || v >= kVariantCount) throw invalid_argument("variant out of range");
@@ -2629,6 +2708,7 @@ double Model::get_stat(const std::string &name) const {
   if (name == "velocity_ms") return stat_velocity_ms_;
   if (name == "pair_launches") return (double)stat_pair_launches_;
   if (name == "resident_ctas") return (double)stat_resident_;
+  if (name == "guard_violations") return (double)const_cast<Model *>(this)->count_guard_violations();
   if (name == "tuned_warps") return tuned_warps_;
   if (name == "tuned_strip") return tuned_strip_;
   if (name == "tune_ms") return stat_tune_ms_;

@@ -310,6 +310,11 @@ class Model {
   unsigned *resident_abort_word_ = nullptr;
   std::map<int, int> resident_capacity_;  // rows per CTA -> co-resident CTAs
   bool resident_timing_ = false;
+  // Debug option "poison_guards": every guard band and pad column the kernels may read but must never use or write
+  // holds a NaN canary (tests/test_gpu_guards.py; stands in for compute-sanitizer, which is closed on the GPU pool).
+  bool poison_ = false;
+  void poison_arrays(bool state_only);
+  long long count_guard_violations();
   DeviceBuffer resident_timing_buf_;
   double stat_resident_phase_[8] = {}, stat_resident_phase_max_[8] = {};
   DeviceBuffer rec_rank_;
