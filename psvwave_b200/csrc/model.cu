@@ -87,35 +87,49 @@ Model::Model(Config cfg, int device, const SlabSpec *slab) : cfg_(std::move(cfg)
   bind();
   // process-wide default of the "resident" option (test suites pin the per-step kernels with PSVWAVE_RESIDENT=0)
   if (const char *e = std::getenv("PSVWAVE_RESIDENT")) resident_ = std::max(-1, std::min(1, std::atoi(e)));
+  try {
+    create_stream_and_events();
+    allocate();
+    initialize_host_tables();
+    build_plans();
+    if (slab_) {
+      const size_t bytes = 2 * 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_ * sizeof(double);
+      halo_send_.allocate(bytes);
+      halo_recv_.allocate(bytes);
+    }
+    PSV_CUDA(cudaStreamSynchronize(stream_));
+  } catch (...) {  // the destructor does not run for a half-built object
+    destroy_stream_and_events();
+    throw;
+  }
+}
+
+void Model::create_stream_and_events() {
   PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   PSV_CUDA(cudaEventCreate(&ev_begin_));
   PSV_CUDA(cudaEventCreate(&ev_end_));
   PSV_CUDA(cudaEventCreate(&ev_t0_));
   PSV_CUDA(cudaEventCreate(&ev_t1_));
-  allocate();
-  initialize_host_tables();
-  build_plans();
-  if (slab_) {
-    const size_t bytes = 2 * 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_ * sizeof(double);
-    halo_send_.allocate(bytes);
-    halo_recv_.allocate(bytes);
-  }
-  PSV_CUDA(cudaStreamSynchronize(stream_));
 }
 
-Model::~Model() {
+void Model::destroy_stream_and_events() {
   cudaSetDevice(device_);
   for (auto &g : graphs_)
     if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+  graphs_.clear();
   for (cudaEvent_t e : prof_events_) cudaEventDestroy(e);
-  for (cudaEvent_t e : {slab_done_[0], slab_done_[1], slab_pulled_[0], slab_pulled_[1]})
-    if (e) cudaEventDestroy(e);
-  if (ev_begin_) cudaEventDestroy(ev_begin_);
-  if (ev_end_) cudaEventDestroy(ev_end_);
-  if (ev_t0_) cudaEventDestroy(ev_t0_);
-  if (ev_t1_) cudaEventDestroy(ev_t1_);
+  prof_events_.clear();
+  for (cudaEvent_t *e : {&slab_done_[0], &slab_done_[1], &slab_pulled_[0], &slab_pulled_[1], &ev_begin_, &ev_end_,
+                         &ev_t0_, &ev_t1_})
+    if (*e) {
+      cudaEventDestroy(*e);
+      *e = nullptr;
+    }
   if (stream_) cudaStreamDestroy(stream_);
+  stream_ = nullptr;
 }
+
+Model::~Model() { destroy_stream_and_events(); }
 
 void Model::bind() const { PSV_CUDA(cudaSetDevice(device_)); }
 
@@ -349,11 +363,8 @@ Model::Model(const Model &o) : Model(o, o.device_, true) {}
 
 Model::Model(const Model &o, int device, bool with_snapshots) : cfg_(o.cfg_), device_(device) {
   bind();
-  PSV_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-  PSV_CUDA(cudaEventCreate(&ev_begin_));
-  PSV_CUDA(cudaEventCreate(&ev_end_));
-  PSV_CUDA(cudaEventCreate(&ev_t0_));
-  PSV_CUDA(cudaEventCreate(&ev_t1_));
+  try {
+  create_stream_and_events();
   slab_ = o.slab_;
   x_off_ = o.x_off_;
   nx_global_ = o.nx_global_;
@@ -421,6 +432,10 @@ Model::Model(const Model &o, int device, bool with_snapshots) : cfg_(o.cfg_), de
     for (int s = 0; s < cfg_.n_shots; ++s) dcopy(o.snapshots_[s], snapshots_[s]);
   build_plans();
   PSV_CUDA(cudaDeviceSynchronize());
+  } catch (...) {  // the destructor does not run for a half-built object
+    destroy_stream_and_events();
+    throw;
+  }
 }
 
 // ---- device-to-device transfers between the replicas of one object (psv::DeviceGroup, multi.cu) ----
@@ -2635,6 +2650,7 @@ void Model::set_option(const std::string &name, long long v) {
     resident_ = (int)v;
   } else if (name == "resident_timing") {
     resident_timing_ = v != 0;
+
 
   } else if (name == "resident_rows") {
     if (v < 0 || v == 1) throw invalid_argument("resident_rows must be 0 (auto) or >= 2");

@@ -178,6 +178,8 @@ class Model {
     std::vector<int> op_row_start_host;
   };
 
+  void create_stream_and_events();
+  void destroy_stream_and_events();
   void allocate();
   void initialize_host_tables();
   void build_plans();

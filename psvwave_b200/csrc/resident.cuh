@@ -326,65 +326,62 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       const bool publish = step + 1 < a.nsteps;
       uint4 *pk = a.packets + (size_t)((step + 1) & 1) * 2 * field_packets;
       const unsigned flag = a.flag_base + (unsigned)(step + 1);
-      for (int i = tid; i < own * P2; i += nthreads) {
+      // one (z-pair, field) per thread -- all vx pairs first, then all vz pairs, so a warp never holds both: the two
+      // fields read disjoint stencil inputs, and twice as many warps share this latency-bound phase
+      const int pairs = own * P2;
+      for (int w = tid; w < 2 * pairs; w += nthreads) {
+        const int fz = w >= pairs, i = w - fz * pairs;  // fz: 0 = vx, 1 = vz
         const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
         const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
         const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
         const int v = (jr + 4) * P2 + kp;
-        double2 vx = tvx[v], vz = tvz[v];
+        double2 *tile = fz ? tvz : tvx;
+        double2 val = tile[v];
         const double2 b = tb[i];
         if (rowok && (za || zb)) {
           const int s = (jr + 2) * P2 + kp;  // stress-tile index of (x, kp)
-          const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
-          const double2 xz_m1 = txz[s - P2], xz_0 = txz[s], xz_p1 = txz[s + P2], xz_p2 = txz[s + 2 * P2];
-          const double2 xzL = txz[s - 1], xzR = txz[s + 1];
-          const double2 zz_0 = tzz[s], zzL = tzz[s - 1], zzR = tzz[s + 1];
           const double tr = ttr[jr + 2];
           const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
-          if (za) {
-            const double dxm_txx = diff4<M>(c.k, xx_0.x, xx_m1.x, xx_m2.x, xx_p1.x);
-            const double dzm_txz = diff4<M>(c.k, xz_0.x, xzL.y, xzL.x, xz_0.y);
-            const double dxp_txz = diff4<M>(c.k, xz_p1.x, xz_0.x, xz_m1.x, xz_p2.x);
-            const double dzp_tzz = diff4<M>(c.k, zz_0.y, zz_0.x, zzL.y, zzR.x);
-            velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.x, dmin2(tr, tz.x), vx.x, vz.x);
-          }
-          if (zb) {
-            const double dxm_txx = diff4<M>(c.k, xx_0.y, xx_m1.y, xx_m2.y, xx_p1.y);
-            const double dzm_txz = diff4<M>(c.k, xz_0.y, xz_0.x, xzL.y, xzR.x);
-            const double dxp_txz = diff4<M>(c.k, xz_p1.y, xz_0.y, xz_m1.y, xz_p2.y);
-            const double dzp_tzz = diff4<M>(c.k, zzR.x, zz_0.y, zz_0.x, zzR.y);
-            velocity_update<M>(c.k, dxm_txx, dzm_txz, dxp_txz, dzp_tzz, b.y, dmin2(tr, tz.y), vx.y, vz.y);
+          const double tpa = dmin2(tr, tz.x), tpb = dmin2(tr, tz.y);
+          if (!fz) {  // vx: D-x txx + D-z txz
+            const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
+            const double2 xz_0 = txz[s], xzL = txz[s - 1], xzR = txz[s + 1];
+            if (za)
+              val.x = velocity_component<M>(c.k, diff4<M>(c.k, xx_0.x, xx_m1.x, xx_m2.x, xx_p1.x),
+                                            diff4<M>(c.k, xz_0.x, xzL.y, xzL.x, xz_0.y), b.x, tpa, val.x);
+            if (zb)
+              val.y = velocity_component<M>(c.k, diff4<M>(c.k, xx_0.y, xx_m1.y, xx_m2.y, xx_p1.y),
+                                            diff4<M>(c.k, xz_0.y, xz_0.x, xzL.y, xzR.x), b.y, tpb, val.y);
+          } else {  // vz: D+x txz + D+z tzz
+            const double2 xz_m1 = txz[s - P2], xz_0 = txz[s], xz_p1 = txz[s + P2], xz_p2 = txz[s + 2 * P2];
+            const double2 zz_0 = tzz[s], zzL = tzz[s - 1], zzR = tzz[s + 1];
+            if (za)
+              val.x = velocity_component<M>(c.k, diff4<M>(c.k, xz_p1.x, xz_0.x, xz_m1.x, xz_p2.x),
+                                            diff4<M>(c.k, zz_0.y, zz_0.x, zzL.y, zzR.x), b.x, tpa, val.x);
+            if (zb)
+              val.y = velocity_component<M>(c.k, diff4<M>(c.k, xz_p1.y, xz_0.y, xz_m1.y, xz_p2.y),
+                                            diff4<M>(c.k, zzR.x, zz_0.y, zz_0.x, zzR.y), b.y, tpb, val.y);
           }
         }
-        for (int q = head[i]; q >= 0; q = s_next[q]) {  // this pair's injections, in list order
+        for (int q = head[i]; q >= 0; q = s_next[q]) {  // this pair's injections, in list order; my field's among them
           const int meta = s_meta[q];
           const double bb = (meta & 1) ? b.y : b.x;
+          double &t = (meta & 1) ? val.y : val.x;
           if (fwd) {
+            if (((meta >> 1) & 1) != fz) continue;
             const double amp = M::kExact ? __ddiv_rn(__dmul_rn(s_amp[q], bb), s_d4[q])
                                          : __dmul_rn(__dmul_rn(s_amp[q], bb), s_rd4[q]);
-            double &t = (meta & 2) ? ((meta & 1) ? vz.y : vz.x) : ((meta & 1) ? vx.y : vx.x);
             t = (meta & 4) ? __dsub_rn(t, amp) : __dadd_rn(t, amp);
           } else {
-            const double dtb = __dmul_rn(c.dt, bb);
-            const double ax = M::kExact ? __ddiv_rn(__dmul_rn(dtb, s_amp[q]), c.dxdz)
-                                        : __dmul_rn(__dmul_rn(dtb, s_amp[q]), c.rdxdz);
-            const double az = M::kExact ? __ddiv_rn(__dmul_rn(dtb, s_amp2[q]), c.dxdz)
-                                        : __dmul_rn(__dmul_rn(dtb, s_amp2[q]), c.rdxdz);
-            double &tx = (meta & 1) ? vx.y : vx.x, &tzv = (meta & 1) ? vz.y : vz.x;
-            tx = __dadd_rn(tx, ax);
-            tzv = __dadd_rn(tzv, az);
+            const double dtb = __dmul_rn(c.dt, bb), src = fz ? s_amp2[q] : s_amp[q];
+            t = __dadd_rn(t, M::kExact ? __ddiv_rn(__dmul_rn(dtb, src), c.dxdz) : __dmul_rn(__dmul_rn(dtb, src), c.rdxdz));
           }
         }
-        tvx[v] = vx;
-        tvz[v] = vz;
+        tile[v] = val;
         if (publish && (jr < 3 || jr >= own - 3) && z0 < nz) {  // rows a neighbour reads (state S_{step+1})
-          uint4 *px = pk + (size_t)x * ld + z0, *pz = px + field_packets;
-          st_packet(px, vx.x, flag);
-          st_packet(pz, vz.x, flag);
-          if (z0 + 1 < nz) {
-            st_packet(px + 1, vx.y, flag);
-            st_packet(pz + 1, vz.y, flag);
-          }
+          uint4 *p0 = pk + (size_t)fz * field_packets + (size_t)x * ld + z0;
+          st_packet(p0, val.x, flag);
+          if (z0 + 1 < nz) st_packet(p0 + 1, val.y, flag);
         }
       }
     }

@@ -98,21 +98,26 @@ __device__ __forceinline__ void stress_update(const SweepConsts &k, double dxp_v
   txz = stress_txz<M>(k, dzp_vx, dxm_vz, mu, tp, txz);
 }
 
-// Velocity update of one point (src/fdModel.cpp:661-676); b = 1/rho (b_vx == b_vz).
+// Velocity update of one point (src/fdModel.cpp:661-676); b = 1/rho (b_vx == b_vz).  Both components have the form
+// v = tp * (v + b*sdt * (dx_term/dx + dz_term/dz)):  vx: dx_term = D-x txx, dz_term = D-z txz;
+// vz: dx_term = D+x txz, dz_term = D+z tzz.
+template <class M>
+__device__ __forceinline__ double velocity_component(const SweepConsts &k, double dx_term, double dz_term, double b,
+                                                     double tp, double v) {
+  if (M::kExact) {
+    const double bs = M::mul(b, k.sdt);
+    return M::mul(tp, M::add(v, M::mul(bs, M::add(M::div(dx_term, k.dx), M::div(dz_term, k.dz)))));
+  }
+  const double bs = __dmul_rn(b, k.sdt);
+  return __dmul_rn(tp, __fma_rn(bs, __fma_rn(dx_term, k.rdx, __dmul_rn(dz_term, k.rdz)), v));
+}
 //   dxm_txx = D-x txx, dzm_txz = D-z txz, dxp_txz = D+x txz, dzp_tzz = D+z tzz
 template <class M>
 __device__ __forceinline__ void velocity_update(const SweepConsts &k, double dxm_txx, double dzm_txz,
                                                 double dxp_txz, double dzp_tzz, double b, double tp,
                                                 double &vx, double &vz) {
-  if (M::kExact) {
-    const double bs = M::mul(b, k.sdt);
-    vx = M::mul(tp, M::add(vx, M::mul(bs, M::add(M::div(dxm_txx, k.dx), M::div(dzm_txz, k.dz)))));
-    vz = M::mul(tp, M::add(vz, M::mul(bs, M::add(M::div(dxp_txz, k.dx), M::div(dzp_tzz, k.dz)))));
-  } else {
-    const double bs = __dmul_rn(b, k.sdt);
-    vx = __dmul_rn(tp, __fma_rn(bs, __fma_rn(dxm_txx, k.rdx, __dmul_rn(dzm_txz, k.rdz)), vx));
-    vz = __dmul_rn(tp, __fma_rn(bs, __fma_rn(dxp_txz, k.rdx, __dmul_rn(dzp_tzz, k.rdz)), vz));
-  }
+  vx = velocity_component<M>(k, dxm_txx, dzm_txz, b, tp, vx);
+  vz = velocity_component<M>(k, dxp_txz, dzp_tzz, b, tp, vz);
 }
 
 // Sensitivity-kernel accumulation of one point (src/fdModel.cpp:832-858): forward snapshot
