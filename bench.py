@@ -222,12 +222,15 @@ def cpu_sample_run(nt: int = NT_SAMPLE, geom=GEOM, steps: int = 1, warmup: int =
     return out
 
 
-def gpu_parity(ref: dict) -> dict:
-    """The CUDA path on the sample the reference just ran (same .ini, same medium, observed data zero):
-    relative L2 differences of what the hot path produces."""
+def gpu_parity(ref: dict, options=()) -> dict:
+    """The CUDA path (with the solver options of this run) on the sample the reference just ran (same .ini, same
+    medium, observed data zero): relative L2 differences of what the hot path produces."""
     import psvwave_b200
     from psvwave_b200 import _array_ids  # noqa: F401  (name -> psv_array id)
     m = psvwave_b200.fdModel(ref["ini"])
+    for kv in options:
+        k, v = kv.split("=")
+        m._set_option(k, int(v))
     m.set_parameter_fields(*marmousi_like(m.nx, m.nz))
     zero = np.zeros((1, m.nr, m.nt))
     m.set_observed_data(zero, zero)
@@ -249,7 +252,8 @@ def gpu_parity(ref: dict) -> dict:
                      ("lambda_kernel", "mu_kernel", "density_l_kernel")])
     return {"against": ref["kind"], "nt": ref["nt"], "rel_l2_ux": rel(ux, a["ux"]), "rel_l2_uz": rel(uz, a["uz"]),
             "rel_l2_kernels": rel(kern, a["kernels"]), "rel_l2_gradient": rel(m.get_gradient_vector(), a["gradient"]),
-            "rel_misfit": abs(m.misfit - a["misfit"]) / abs(a["misfit"]), "tolerance": 1e-10}
+            "rel_misfit": abs(m.misfit - a["misfit"]) / abs(a["misfit"]),
+            "tolerance": 1e-3 if m._get_option("fp32") else 1e-10}
 
 
 def sample_config() -> dict:
@@ -545,7 +549,7 @@ def run_ours(args) -> None:
             r = cpu_sample_run(NT_SAMPLE, keep=True)
             cpu = {"value": r["rate"], "unit": "updates/s", "cores": r["threads"], "kind": r["kind"],
                    "sample": r["sample"]}
-            parity = gpu_parity(r)
+            parity = gpu_parity(r, args.option)
         cfg_out = sample_config()
         cfg_out.update({"grid": [nx, nz], "nt": nt, "snapshot_interval": m.snapshot_interval,
                         "shots_per_gpu_per_step": 1, "receivers": m.nr,

@@ -10,7 +10,9 @@
 //
 // Same march as fused.cuh (a warp owns 28 z-pairs of a strip of rows, rolling register windows
 // along x, z-neighbours by warp shuffle, new stresses consumed from registers), restated on
-// float2 pairs with loads straight from global memory; see fused.cuh for the geometry.
+// float2 pairs; see fused.cuh for the geometry.  Two row sources, like variants 2 and 3 of the FP64 march: loads straight
+// from global memory with the next row's loads issued one iteration ahead (fused32_step_kernel), and a TMA bulk-copy
+// ring filled by a producer warp (fused32_pipe_kernel, the default: "variant" 3).
 #pragma once
 
 #include "fused.cuh"
@@ -51,19 +53,69 @@ __device__ __forceinline__ float taper_axis_f(const double *__restrict__ table, 
   return (float)taper_axis(table, np, i, n);
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, const FusedModel32 *__restrict__ models) {
-  const int lane = threadIdx.x & 31;
-  const int zw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (zw >= c.n_zwarps) return;  // warp-uniform
-  const FusedModel32 &m = models[blockIdx.z];
-  const int kp = zw * kFusedOwnedPairs - 2 + lane;
-  const int xs = blockIdx.y * c.strip;
-  const int xe = min(xs + c.strip, c.g.nx);
+struct Row32 {  // what one row of the march consumes: vx of row j+2, vz of row j+1, the rest of row j (b of row j-2)
+  float2 vx_p2, vz_p1, txx, tzz, txz, lm, mu, b;
+};
+
+// Row source 1: global memory, software-pipelined one row ahead.
+struct GlobalRows32 {
+  const float *ovx, *ovz, *oxx, *ozz, *oxz, *lm, *mu, *b;
+  long long ld2n;
+  Row32 next;
+  __device__ __forceinline__ void load(long long r) {  // rows past the strip end fall into the guard band: harmless
+    next.vx_p2 = ld2f(ovx, r + 2 * ld2n);
+    next.vz_p1 = ld2f(ovz, r + ld2n);
+    next.txx = ld2f(oxx, r);
+    next.tzz = ld2f(ozz, r);
+    next.txz = ld2f(oxz, r);
+    next.lm = ld2f(lm, r);
+    next.mu = ld2f(mu, r);
+    next.b = ld2f(b, r - 2 * ld2n);
+  }
+  __device__ __forceinline__ void start(long long r) { load(r); }
+  __device__ __forceinline__ void fetch(long long r, Row32 &d) {
+    d = next;
+    load(r + ld2n);
+  }
+  __device__ __forceinline__ void release() {}
+};
+
+// Row source 2: the shared-memory ring a producer lane fills with bulk-asynchronous copies (8 row segments per slot).
+struct PipeRows32 {
+  const unsigned char *ring;
+  unsigned full0, empty0;
+  int stages, seg, stage_bytes, lane_off, slot;
+  unsigned phase;
+  int lane;
+  __device__ __forceinline__ void start(long long) {}
+  __device__ __forceinline__ void fetch(long long, Row32 &d) {
+    mbar_wait(full0 + 8 * slot, phase);
+    const unsigned char *s = ring + (size_t)slot * stage_bytes + lane_off;
+    d.vx_p2 = *reinterpret_cast<const float2 *>(s);
+    d.vz_p1 = *reinterpret_cast<const float2 *>(s + seg);
+    d.txx = *reinterpret_cast<const float2 *>(s + 2 * seg);
+    d.tzz = *reinterpret_cast<const float2 *>(s + 3 * seg);
+    d.txz = *reinterpret_cast<const float2 *>(s + 4 * seg);
+    d.lm = *reinterpret_cast<const float2 *>(s + 5 * seg);
+    d.mu = *reinterpret_cast<const float2 *>(s + 6 * seg);
+    d.b = *reinterpret_cast<const float2 *>(s + 7 * seg);
+  }
+  __device__ __forceinline__ void release() {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+    if (++slot == stages) {
+      slot = 0;
+      phase ^= 1;
+    }
+  }
+};
+
+// One warp marches rows [xs, xe) for the z-pairs {kp}; lanes 2..29 own their pair.
+template <int MODE, class Rows>
+__device__ __forceinline__ void fused32_march(const FusedCommon &c, const FusedModel32 &m, Rows &rows, const int lane,
+                                              const int kp, const int xs, const int xe, const bool own) {
   const long long ld2n = c.g.ld >> 1;
-  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
-  const float *ovx = m.f[c.parity][0], *ovz = m.f[c.parity][1], *oxx = m.f[c.parity][2], *ozz = m.f[c.parity][3],
-              *oxz = m.f[c.parity][4];
+  const float *ovx = m.f[c.parity][0], *ovz = m.f[c.parity][1];
   float *nvx = m.f[c.parity ^ 1][0], *nvz = m.f[c.parity ^ 1][1], *nxx = m.f[c.parity ^ 1][2],
         *nzz = m.f[c.parity ^ 1][3], *nxz = m.f[c.parity ^ 1][4];
   const Consts32 k{(float)c.k.sdt, (float)c.k.rdx, (float)c.k.rdz, (float)c.k.c1, (float)c.k.c2};
@@ -75,11 +127,46 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
   const bool zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
   const float tza = taper_axis_f(c.taper_table, c.g.np, z0, nz), tzb = taper_axis_f(c.taper_table, c.g.np, z0 + 1, nz);
 
-  bool strip_rec = false, strip_ops = false;
+  // Cursors into the row-sorted point lists (as in fused_march): the row of the next receiver / injection operation
+  // sits in a register, the strip's receivers ride in registers one list entry per lane.
+  int rq = 0, rq_end = 0, oq = 0, oq_end = 0;
   if (c.point_mode != POINT_NONE) {
-    strip_rec = c.rec_row_start[xe] > c.rec_row_start[xs];
-    if (c.point_mode == POINT_FORWARD) strip_ops = c.op_row_start[xe] > c.op_row_start[xs];
+    rq = c.rec_row_start[xs];
+    rq_end = c.rec_row_start[xe];
+    if (c.point_mode == POINT_FORWARD) {
+      oq = c.op_row_start[xs];
+      oq_end = c.op_row_start[xe];
+    }
   }
+  constexpr int kNoRow = 0x7fffffff;
+  int op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
+  int win0 = rq, lx = kNoRow, lz = 0, lid = 0;
+  double lax = 0.0, laz = 0.0;
+  auto load_window = [&]() {
+    const int q = win0 + lane;
+    lx = kNoRow;
+    if (q < rq_end) {
+      lx = c.rec_x[q];
+      lz = c.rec_z[q];
+      lid = c.rec_id[q];
+      if (c.point_mode == POINT_ADJOINT) {
+        const size_t t = (size_t)lid * c.nt + c.it;
+        lax = m.ax[t];
+        laz = m.az[t];
+      }
+    }
+  };
+  if (rq < rq_end) load_window();
+  int rec_next = __shfl_sync(0xffffffffu, lx, 0);
+  auto next_receiver = [&]() {
+    ++rq;
+    if (rq >= rq_end) return kNoRow;
+    if (rq - win0 == 32) {
+      win0 = rq;
+      load_window();
+    }
+    return __shfl_sync(0xffffffffu, lx, rq - win0);
+  };
 
   int j = xs - 2;
   long long r = (long long)j * ld2n + kp;
@@ -90,27 +177,15 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
   float2 xz_m3 = zero2, xz_m2 = zero2, xz_m1 = zero2;
   float2 zz_m2 = zero2, zz_m1 = zero2;
 
-  // software pipeline: the 8 loads of row j+1 are issued before row j is computed, so a warp always
-  // has one row of memory latency in flight (the FP64 default gets the same from its TMA ring)
-  float2 n_vx = ld2f(ovx, r + 2 * ld2n), n_vz = ld2f(ovz, r + ld2n), n_xx = ld2f(oxx, r), n_zz = ld2f(ozz, r),
-         n_xz = ld2f(oxz, r), n_lm = ld2f(m.lm, r), n_mu = ld2f(m.mu, r), n_b = ld2f(m.b, r - 2 * ld2n);
+  rows.start(r);
 #pragma unroll 1
   for (; j < xe + 2; ++j, r += ld2n) {
-    const float2 vx_p2 = n_vx, vz_p1 = n_vz;
-    float2 txx = n_xx, tzz = n_zz, txz = n_xz;
-    const float2 lm = n_lm, mu = n_mu;
-    const float2 b = n_b;
-    {  // rows past the strip end fall into the guard band / the next strip's rows: harmless reads
-      const long long rn = r + ld2n;
-      n_vx = ld2f(ovx, rn + 2 * ld2n);
-      n_vz = ld2f(ovz, rn + ld2n);
-      n_xx = ld2f(oxx, rn);
-      n_zz = ld2f(ozz, rn);
-      n_xz = ld2f(oxz, rn);
-      n_lm = ld2f(m.lm, rn);
-      n_mu = ld2f(m.mu, rn);
-      n_b = ld2f(m.b, rn - 2 * ld2n);
-    }
+    Row32 d;
+    rows.fetch(r, d);
+    const float2 vx_p2 = d.vx_p2, vz_p1 = d.vz_p1;
+    float2 txx = d.txx, tzz = d.tzz, txz = d.txz;
+    const float2 lm = d.lm, mu = d.mu;
+    const float2 b = d.b;
     const bool row_mine = j >= xs && j < xe;  // warp-uniform
     const float tr_j = taper_axis_f(c.taper_table, c.g.np, gx0 + j, gnx),
                 tr_x = taper_axis_f(c.taper_table, c.g.np, gx0 + j - 2, gnx);
@@ -142,15 +217,14 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
           st2s(m.k_mu, r, km);
         }
       }
-      if (c.point_mode == POINT_FORWARD && strip_rec) {  // receiver sampling, running sum in double
-        const int q1 = c.rec_row_start[j + 1];
-        for (int q = c.rec_row_start[j]; q < q1; ++q) {
-          const int z = c.rec_z[q];
+      if (c.point_mode == POINT_FORWARD && j == rec_next) {  // receiver sampling, running sum in double
+        do {
+          const int z = __shfl_sync(0xffffffffu, lz, rq - win0), id = __shfl_sync(0xffffffffu, lid, rq - win0);
           if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
+            const size_t t = (size_t)id * c.nt + c.it;
             const double sx = __ddiv_rn(__dmul_rn(c.dt, (double)((z & 1) ? vx_0.y : vx_0.x)), c.dxdz);
             const double sz = __ddiv_rn(__dmul_rn(c.dt, (double)((z & 1) ? vz_0.y : vz_0.x)), c.dxdz);
-            if (c.it == 0) {
+            if (c.rec_increments || c.it == 0) {  // (no read-modify-write of global memory inside the march)
               m.ux[t] = sx;
               m.uz[t] = sz;
             } else {
@@ -158,9 +232,12 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
               m.uz[t] = __dadd_rn(m.uz[t - 1], sz);
             }
           }
-        }
+          rec_next = next_receiver();
+        } while (rec_next == j);
       }
     }
+
+    rows.release();  // the row's slot of a shared-memory ring can be refilled from here on
 
     {  // ---- stress update of row j ----
       const float vxL_y = shfl_up1f(vx_0.y), vxR_x = shfl_dn1f(vx_0.x), vxR_y = shfl_dn1f(vx_0.y);
@@ -224,10 +301,9 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
         vx.y = ub ? bvx : vx.y;
         vz.y = ub ? bvz : vz.y;
       }
-      if (strip_ops) {  // moment-tensor injection, amplitude in double (src/fdModel.cpp:681-751)
-        const int q1 = c.op_row_start[x + 1];
-        for (int q = c.op_row_start[x]; q < q1; ++q) {
-          const RowOp op = c.ops[q];
+      if (x == op_next) {  // moment-tensor injection, amplitude in double (src/fdModel.cpp:681-751)
+        do {
+          const RowOp op = c.ops[oq];
           if (own && (op.z >> 1) == kp) {
             const double w = c.stf[(size_t)op.source * c.nt + c.it];
             const double bb = (double)((op.z & 1) ? b.y : b.x);
@@ -236,16 +312,17 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
             float &t = op.field == 0 ? (odd ? vx.y : vx.x) : (odd ? vz.y : vz.x);
             t = (float)(op.sign > 0 ? (double)t + amp : (double)t - amp);
           }
-        }
+          ++oq;
+          op_next = oq < oq_end ? c.ops[oq].x : kNoRow;
+        } while (op_next == x);
       }
-      if (c.point_mode == POINT_ADJOINT && strip_rec) {  // adjoint sources at the receivers (:951-958)
-        const int q1 = c.rec_row_start[x + 1];
-        for (int q = c.rec_row_start[x]; q < q1; ++q) {
-          const int z = c.rec_z[q];
+      if (c.point_mode == POINT_ADJOINT && x == rec_next) {  // adjoint sources at the receivers (:951-958)
+        do {
+          const int z = __shfl_sync(0xffffffffu, lz, rq - win0);
+          const double sax = __shfl_sync(0xffffffffu, lax, rq - win0), saz = __shfl_sync(0xffffffffu, laz, rq - win0);
           if (own && (z >> 1) == kp) {
-            const size_t t = (size_t)c.rec_id[q] * c.nt + c.it;
             const double bb = (double)((z & 1) ? b.y : b.x);
-            const double ax = ((c.dt * bb) * m.ax[t]) * c.rdxdz, az = ((c.dt * bb) * m.az[t]) * c.rdxdz;
+            const double ax = ((c.dt * bb) * sax) * c.rdxdz, az = ((c.dt * bb) * saz) * c.rdxdz;
             if (z & 1) {
               vx.y = (float)((double)vx.y + ax);
               vz.y = (float)((double)vz.y + az);
@@ -254,7 +331,8 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
               vz.x = (float)((double)vz.x + az);
             }
           }
-        }
+          rec_next = next_receiver();
+        } while (rec_next == x);
       }
       if (own) {
         st2f(nvx, rv, vx);
@@ -268,6 +346,88 @@ __global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, 
     xz_m3 = xz_m2; xz_m2 = xz_m1; xz_m1 = txz;
     zz_m2 = zz_m1; zz_m1 = tzz;
   }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) fused32_step_kernel(const FusedCommon c, const FusedModel32 *__restrict__ models) {
+  const int lane = threadIdx.x & 31;
+  const int zw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (zw >= c.n_zwarps) return;  // warp-uniform
+  const FusedModel32 &m = models[blockIdx.z];
+  const int kp = zw * kFusedOwnedPairs - 2 + lane;
+  const int xs = blockIdx.y * c.strip;
+  const int xe = min(xs + c.strip, c.g.nx);
+  const long long ld2n = c.g.ld >> 1;
+  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
+  GlobalRows32 rows{m.f[c.parity][0], m.f[c.parity][1], m.f[c.parity][2], m.f[c.parity][3], m.f[c.parity][4],
+                    m.lm, m.mu, m.b, ld2n, Row32{}};
+  fused32_march<MODE>(c, m, rows, lane, kp, xs, xe, own);
+}
+
+// The FP32 march fed by a TMA bulk-copy ring: NW consumer warps (adjacent z-warps of one strip) + one producer warp
+// whose elected lane issues, per row of the march, 8 bulk-asynchronous copies of (NW*28 + 4) float2 pairs into a slot
+// of a `stages`-deep shared-memory ring guarded by full/empty mbarriers -- the design of fused_pipe_kernel (fused.cuh)
+// at half the bytes.  (The correlation rows read their snapshot / Lame-kernel values straight from global memory.)
+template <int NW>
+struct PipeGeom32 {
+  static constexpr int kOwned = NW * kFusedOwnedPairs;
+  static constexpr int kPairs = kOwned + 4;
+  static constexpr int kSeg = kPairs * 8;          // bytes of one row segment (multiple of 16: NW*224 + 32)
+  static constexpr int kStage = kSeg * kPipeArrays;
+};
+
+template <int MODE, int NW>
+__global__ void __launch_bounds__((NW + 1) * 32) fused32_pipe_kernel(const FusedCommon c,
+                                                                     const FusedModel32 *__restrict__ models,
+                                                                     const int stages) {
+  using G = PipeGeom32<NW>;
+  extern __shared__ __align__(128) unsigned char psv_smem[];
+  unsigned long long *bars = reinterpret_cast<unsigned long long *>(psv_smem);  // [stages] full, [stages] empty
+  unsigned char *ring = psv_smem + 128 * ((2 * stages * 8 + 127) / 128);
+  const unsigned full0 = smem_u32(bars), empty0 = full0 + 8 * stages;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, NW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const FusedModel32 &m = models[blockIdx.z];
+  const long long ld2n = c.g.ld >> 1;
+  const int xs = blockIdx.y * c.strip;
+  const int xe = min(xs + c.strip, c.g.nx);
+  const int kp_tile = blockIdx.x * G::kOwned - 2;  // first pair of the CTA's row segment
+  if (warp == NW) {
+    if (lane == 0) {
+      const float *src[kPipeArrays] = {m.f[c.parity][0], m.f[c.parity][1], m.f[c.parity][2], m.f[c.parity][3],
+                                       m.f[c.parity][4], m.lm,           m.mu,             m.b};
+      const long long row_off[kPipeArrays] = {2, 1, 0, 0, 0, 0, 0, -2};  // row of each array relative to j
+      int slot = 0;
+      unsigned phase = 0;
+      const unsigned ring_u32 = smem_u32(ring);
+      for (int j = xs - 2; j < xe + 2; ++j) {
+        mbar_wait(empty0 + 8 * slot, phase ^ 1);
+        const unsigned bar = full0 + 8 * slot;
+        mbar_expect_tx(bar, G::kStage);
+        const unsigned dst = ring_u32 + slot * G::kStage;
+#pragma unroll
+        for (int a = 0; a < kPipeArrays; ++a)
+          bulk_g2s(dst + a * G::kSeg,
+                   reinterpret_cast<const float2 *>(src[a]) + ((long long)j + row_off[a]) * ld2n + kp_tile, G::kSeg, bar);
+        if (++slot == stages) {
+          slot = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    return;
+  }
+  PipeRows32 rows{ring, full0, empty0, stages, G::kSeg, G::kStage, (warp * kFusedOwnedPairs + lane) * 8, 0, 0u, lane};
+  const int kp = kp_tile + warp * kFusedOwnedPairs + lane;
+  const bool own = lane >= 2 && lane < 30 && kp < (int)ld2n;
+  fused32_march<MODE>(c, m, rows, lane, kp, xs, xe, own);
 }
 
 }  // namespace psv

@@ -2,6 +2,7 @@
 #include <type_traits>
 
 #include "fused.cuh"
+#include "fused32.cuh"
 #include "launchers.hpp"
 #include "model.hpp"
 
@@ -71,6 +72,33 @@ int pipe_occupancy(int nw, size_t smem) {
     PSV_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_pipe_kernel<FastMath, MODE_PLAIN, NW>,
                                                            (NW + 1) * 32, smem));
     return per_sm;
+  });
+}
+
+// ---- the FP32 march on the same ring (fused32.cuh) ----
+namespace {
+template <int MODE, int NW>
+void launch32_k(const FusedCommon &fc, const FusedModel32 *models, dim3 grid, int stages, size_t smem, cudaStream_t st) {
+  static SmemOptIn opt_in;  // per instantiation
+  opt_in.ensure(fused32_pipe_kernel<MODE, NW>, smem);
+  fused32_pipe_kernel<MODE, NW><<<grid, (NW + 1) * 32, smem, st>>>(fc, models, stages);
+}
+}  // namespace
+
+size_t pipe32_smem_bytes(int nw, int stages) {
+  return with_pipe_warps(nw, [&](auto w) {
+    return 128 * ((2 * (size_t)stages * 8 + 127) / 128) + (size_t)stages * PipeGeom32<decltype(w)::value>::kStage;
+  });
+}
+
+void launch_pipe32(int nw, int mode, const FusedCommon &fc, const FusedModel32 *models, dim3 grid, int stages,
+                   size_t smem, cudaStream_t st) {
+  with_pipe_warps(nw, [&](auto w) {
+    constexpr int NW = decltype(w)::value;
+    if (mode == MODE_SNAPSHOT) launch32_k<MODE_SNAPSHOT, NW>(fc, models, grid, stages, smem, st);
+    else if (mode == MODE_ACCUMULATE) launch32_k<MODE_ACCUMULATE, NW>(fc, models, grid, stages, smem, st);
+    else launch32_k<MODE_PLAIN, NW>(fc, models, grid, stages, smem, st);
+    return 0;
   });
 }
 

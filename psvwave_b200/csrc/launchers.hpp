@@ -48,6 +48,11 @@ int pipe_occupancy(int nw, size_t smem);
 void launch_pipe(bool exact, int nw, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages,
                  size_t smem, cudaStream_t st);
 
+// ---- the optional FP32 wavefield mode on the same ring (fused32.cuh), its default ----
+size_t pipe32_smem_bytes(int nw, int stages);
+void launch_pipe32(int nw, int mode, const FusedCommon &fc, const FusedModel32 *models, dim3 grid, int stages,
+                   size_t smem, cudaStream_t st);
+
 // ---- variant 4: two time steps per launch (pair.cuh) ----
 size_t pair_smem(int nw, int stages);
 void launch_pair(bool exact, int nw, int mode, const FusedCommon &fc, const FusedModel *models, dim3 grid, int stages,

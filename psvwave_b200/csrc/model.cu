@@ -922,7 +922,7 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
 // 0, which that loop writes again): the warp that carries them is the critical path of its CTA row.
 void Model::tune_pipe_geometry(int i_shot, int point_mode) {
   const int batch = 1 + (int)batch_followers_.size();
-  if (variant_ != 3 || fp32_ || tune_ == 0 || pipe_warps_ != 0 || fused_strip_ != 0) return;
+  if (variant_ != 3 || tune_ == 0 || pipe_warps_ != 0 || fused_strip_ != 0) return;
   if (tune_ < 0 && (long long)cfg_.nx * cfg_.nz * batch < (1ll << 21)) return;  // small grids: latency rules, see above
   if (tuned_strip_ > 0 && tuned_batch_ == batch) return;
   bind();
@@ -1089,6 +1089,19 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   const int batch = 1 + (int)batch_followers_.size();
   if (fp32_) {
     if (slab_) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
+    if (variant_ == 3) {  // the march fed by the TMA ring, geometry like the FP64 default (option, measured, or formula)
+      int tiles = 0, strip = 0;
+      size_t smem64 = 0;
+      pipe_geometry(batch, &tiles, &strip, &smem64);
+      const int nw = pipe_warps();
+      fc.strip = strip;
+      dim3 grid(tiles, (c.nx + strip - 1) / strip, batch);
+      launch_pipe32(nw, mode, fc, fused_model32_.as<FusedModel32>(), grid, pipe_stages_,
+                    pipe32_smem_bytes(nw, pipe_stages_), stream_);
+      cur_ ^= 1;
+      ++stat_launches_;
+      return;
+    }
     const int wpb = 4;
     if (fused_strip_ > 0) {
       fc.strip = fused_strip_;
@@ -1297,7 +1310,7 @@ struct Profiler {  // CUDA events around sampled sweep launches
 
 // The fused FP64 marches (variants 2, 3, 4) store receiver increments; the running sum over time
 // is taken once after the time loop (same order, same rounding as the reference's in-loop sum).
-bool Model::receiver_increments() const { return !fp32_ && variant_ >= 2; }
+bool Model::receiver_increments() const { return variant_ >= 2; }
 
 void Model::finish_receivers(int i_shot, cudaStream_t st) {
   const Config &c = cfg_;
