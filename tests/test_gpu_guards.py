@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 KERNELS = ("lambda_kernel", "mu_kernel", "density_l_kernel", "vp_kernel", "vs_kernel", "density_v_kernel")
 FAMILIES = [dict(variant=3), dict(variant=3, pipe_warps=8, pipe_stages=3), dict(variant=3, pipe_warps=4, fused_strip=5),
             dict(variant=2), dict(variant=4), dict(variant=1), dict(variant=0), dict(resident=1),
-            dict(resident=1, resident_rows=7), dict(variant=3, exact=1), dict(variant=3, fp32=1)]
+            dict(resident=1, resident_rows=7), dict(variant=3, exact=1), dict(variant=3, fp32=1), dict(variant=2, fp32=1)]
 
 
 def run(ini, medium, obs, poison, **options):
