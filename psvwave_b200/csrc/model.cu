@@ -996,6 +996,13 @@ void Model::tune_pipe_geometry(int i_shot, int point_mode) {
   tuned_strip_ = best_s;
   tuned_batch_ = batch;
   cur_ = cur0;
+  // the caller zeroes THIS model's state next; the other members of an ensemble were zeroed before it was called
+  PSV_CUDA(cudaStreamSynchronize(stream_));
+  for (Model *f : batch_followers_) {
+    f->zero_dynamic_fields();
+    PSV_CUDA(cudaStreamSynchronize(f->stream_));
+  }
+  bind();
   stat_launches_ = launches0;
   drop_graphs();
   stat_tune_ms_ = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
@@ -2618,8 +2625,14 @@ void Model::load_vector(const std::string &path, bool verbose, double *out, size
 // options / statistics
 // ---------------------------------------------------------------------------------------------
 void Model::set_option(const std::string &name, long long v) {
-  tuned_warps_ = tuned_strip_ = tuned_batch_ = 0;  // measured for the options that were in force
-  pipe_resident_ = 0;
+  static const char *const kNeutral[] = {"profile", "graph", "resident", "resident_rows", "resident_timing",
+                                         "poison_guards"};  // do not change what a step launch runs or costs
+  bool neutral = false;
+  for (const char *n : kNeutral) neutral = neutral || name == n;
+  if (!neutral) {
+    tuned_warps_ = tuned_strip_ = tuned_batch_ = 0;  // measured for the options that were in force
+    pipe_resident_ = 0;
+  }
   if (name == "poison_guards") {
     poison_ = v != 0;
     if (poison_) {

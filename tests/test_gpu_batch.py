@@ -13,7 +13,8 @@ from oracle.oracle import OracleModel
 pytestmark = pytest.mark.gpu
 
 KERNELS = ("lambda_kernel", "mu_kernel", "density_l_kernel")
-BATCH_VARIANTS = [dict(variant=2), dict(variant=3), dict(variant=3, pipe_warps=4), dict(variant=3, pipe_warps=8), dict(variant=4)]
+BATCH_VARIANTS = [dict(variant=2), dict(variant=3), dict(variant=3, pipe_warps=4), dict(variant=3, pipe_warps=8), dict(variant=4),
+                  dict(variant=3, tune=1, graph=0)]  # launch geometry measured on the ensemble's own state arrays first
 
 
 def fd(ini, **options):
