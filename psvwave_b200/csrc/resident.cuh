@@ -164,7 +164,8 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
   }
 
   // optional phase timing (option "resident_timing"): thread 0 accumulates clock64 deltas per phase
-  long long t_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  __shared__ long long t_acc[8];
+  if (tid < 8) t_acc[tid] = 0;
   long long t_last = clock64();
 #define TICK(k)                      \
   if (a.timing && tid == 0) {        \
@@ -224,6 +225,57 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
   };
 
   __syncthreads();
+  // What a thread does in the two update phases never changes over the time loop: tile indices, frame masks and taper
+  // values of its first item of each phase ride in registers (no integer divisions, table lookups or mask logic per
+  // step: three quarters of the instructions of a step were such overhead); further items of wide strips are worked
+  // out on the fly.
+  struct StressItem {
+    int v;           // velocity-tile index of (j, kp)
+    unsigned flags;  // 1 update, 2 lower column inside the frame, 4 upper column, 8 txx, 16 tzz, 32 txz
+    double tpa, tpb;
+  };
+  auto stress_item = [&](int i) {
+    StressItem it;
+    const int jr = i / P2, kp = i - jr * P2, j = xs - 2 + jr, z0 = 2 * kp;
+    const bool rowok = gx0 + j >= 2 && gx0 + j < gnx - 2;
+    const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
+    it.flags = (rowok && (za || zb) ? 1u : 0u) | (za ? 2u : 0u) | (zb ? 4u : 0u) | (jr <= own + 2 ? 8u : 0u) |
+               (jr >= 2 && jr < own + 2 ? 16u : 0u) | (jr >= 1 ? 32u : 0u);
+    it.v = (jr + 2) * P2 + kp;
+    const double tr = ttr[jr];
+    it.tpa = dmin2(tr, ttz[z0]);
+    it.tpb = dmin2(tr, ttz[z0 + 1]);
+    return it;
+  };
+  struct VelItem {
+    int i, v, s, pk;  // own-pair index, velocity- and stress-tile index, packet offset inside a parity buffer
+    unsigned flags;   // 1 update, 2 lower column, 4 upper column, 8 field is vz, 16 row is read by a neighbour, 32 upper
+                      // column inside the grid
+    double tpa, tpb;
+  };
+  auto vel_item = [&](int w) {
+    VelItem it;
+    const int pairs = own * P2;
+    const int fz = w >= pairs, i = w - fz * pairs;
+    const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
+    const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
+    const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
+    it.i = i;
+    it.v = (jr + 4) * P2 + kp;
+    it.s = (jr + 2) * P2 + kp;
+    it.pk = (int)(fz * field_packets) + x * ld + z0;
+    it.flags = (rowok && (za || zb) ? 1u : 0u) | (za ? 2u : 0u) | (zb ? 4u : 0u) | (fz ? 8u : 0u) |
+               ((jr < 3 || jr >= own - 3) && z0 < nz ? 16u : 0u) | (z0 + 1 < nz ? 32u : 0u);
+    const double tr = ttr[jr + 2];
+    it.tpa = dmin2(tr, ttz[z0]);
+    it.tpb = dmin2(tr, ttz[z0 + 1]);
+    return it;
+  };
+  const int n_stress = (own + 4) * P2, n_vel = 2 * own * P2;
+  StressItem s_first{0, 0u, 0.0, 0.0};
+  VelItem v_first{0, 0, 0, 0, 0u, 0.0, 0.0};
+  if (tid < n_stress) s_first = stress_item(tid);
+  if (tid < n_vel) v_first = vel_item(tid);
   side_effects(fwd ? 0 : a.nsteps - 1);
 
   for (int step = 0; step < a.nsteps; ++step) {
@@ -271,16 +323,13 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     TICK(0);
     // 2. the stress components the own velocities read, in place: txx rows [xs-2, xe], tzz own rows, txz rows
     //    [xs-1, xe+1]
-    for (int i = tid; i < (own + 4) * P2; i += nthreads) {
-      const int jr = i / P2, kp = i - jr * P2, j = xs - 2 + jr, z0 = 2 * kp;
-      const bool rowok = gx0 + j >= 2 && gx0 + j < gnx - 2;
-      const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
-      if (!rowok || !(za || zb)) continue;  // frame rows / pad pairs keep their values
-      const bool do_xx = jr <= own + 2, do_zz = jr >= 2 && jr < own + 2, do_xz = jr >= 1;
-      const int v = (jr + 2) * P2 + kp;  // velocity-tile index of (j, kp)
-      const double tr = ttr[jr];
-      const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
-      const double tpa = dmin2(tr, tz.x), tpb = dmin2(tr, tz.y);
+    for (int i = tid; i < n_stress; i += nthreads) {
+      const StressItem it = i == tid ? s_first : stress_item(i);
+      if (!(it.flags & 1u)) continue;  // frame rows / pad pairs keep their values
+      const bool za = it.flags & 2u, zb = it.flags & 4u;
+      const bool do_xx = it.flags & 8u, do_zz = it.flags & 16u, do_xz = it.flags & 32u;
+      const int v = it.v;
+      const double tpa = it.tpa, tpb = it.tpb;
       const double2 lm = tlm[i], mu = tmu[i];
       if (do_xx) {  // D+x vx and D-z vz feed txx and tzz
         const double2 vx_m1 = tvx[v - P2], vx_0 = tvx[v], vx_p1 = tvx[v + P2], vx_p2 = tvx[v + 2 * P2];
@@ -328,21 +377,16 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       const unsigned flag = a.flag_base + (unsigned)(step + 1);
       // one (z-pair, field) per thread -- all vx pairs first, then all vz pairs, so a warp never holds both: the two
       // fields read disjoint stencil inputs, and twice as many warps share this latency-bound phase
-      const int pairs = own * P2;
-      for (int w = tid; w < 2 * pairs; w += nthreads) {
-        const int fz = w >= pairs, i = w - fz * pairs;  // fz: 0 = vx, 1 = vz
-        const int jr = i / P2, kp = i - jr * P2, x = xs + jr, z0 = 2 * kp;
-        const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
-        const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
-        const int v = (jr + 4) * P2 + kp;
+      for (int w = tid; w < n_vel; w += nthreads) {
+        const VelItem it = w == tid ? v_first : vel_item(w);
+        const int i = it.i, v = it.v;
+        const bool fz = it.flags & 8u, za = it.flags & 2u, zb = it.flags & 4u;
         double2 *tile = fz ? tvz : tvx;
         double2 val = tile[v];
         const double2 b = tb[i];
-        if (rowok && (za || zb)) {
-          const int s = (jr + 2) * P2 + kp;  // stress-tile index of (x, kp)
-          const double tr = ttr[jr + 2];
-          const double2 tz = *reinterpret_cast<const double2 *>(ttz + z0);
-          const double tpa = dmin2(tr, tz.x), tpb = dmin2(tr, tz.y);
+        if (it.flags & 1u) {
+          const int s = it.s;  // stress-tile index of (x, kp)
+          const double tpa = it.tpa, tpb = it.tpb;
           if (!fz) {  // vx: D-x txx + D-z txz
             const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
             const double2 xz_0 = txz[s], xzL = txz[s - 1], xzR = txz[s + 1];
@@ -368,7 +412,7 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
           const double bb = (meta & 1) ? b.y : b.x;
           double &t = (meta & 1) ? val.y : val.x;
           if (fwd) {
-            if (((meta >> 1) & 1) != fz) continue;
+            if ((((meta >> 1) & 1) != 0) != fz) continue;
             const double amp = M::kExact ? __ddiv_rn(__dmul_rn(s_amp[q], bb), s_d4[q])
                                          : __dmul_rn(__dmul_rn(s_amp[q], bb), s_rd4[q]);
             t = (meta & 4) ? __dsub_rn(t, amp) : __dadd_rn(t, amp);
@@ -378,10 +422,10 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
           }
         }
         tile[v] = val;
-        if (publish && (jr < 3 || jr >= own - 3) && z0 < nz) {  // rows a neighbour reads (state S_{step+1})
-          uint4 *p0 = pk + (size_t)fz * field_packets + (size_t)x * ld + z0;
+        if (publish && (it.flags & 16u)) {  // rows a neighbour reads (state S_{step+1})
+          uint4 *p0 = pk + it.pk;
           st_packet(p0, val.x, flag);
-          if (z0 + 1 < nz) st_packet(p0 + 1, val.y, flag);
+          if (it.flags & 32u) st_packet(p0 + 1, val.y, flag);
         }
       }
     }
