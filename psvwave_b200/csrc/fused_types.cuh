@@ -72,7 +72,8 @@ struct FusedModel32 {  // per-model pointers of the FP32 mode
 
 // ---- resident whole-loop kernel (resident.cuh) ----
 constexpr int kResidentThreads = 512;
-constexpr int kResidentMaxOps = 128;  // injection operations (forward) / receivers (adjoint) of one strip
+constexpr int kResidentMaxOps = 128;
+constexpr size_t kResidentSmemBudget = 232448 - 8192;  // dynamic shared memory of the loop kernel (its static arrays aside)  // injection operations (forward) / receivers (adjoint) of one strip
 
 struct ResidentArgs {
   FusedCommon c;  // geometry, constants (k.sdt carries the sign of the time direction), point lists, window
@@ -97,7 +98,8 @@ struct ResidentArgs {
 // results are discarded).
 struct ResidentLayout {
   int pitch, rows;
-  int vx, vz, xx, zz, xz, lm, mu, b, tz, tr, head, end;
+  int vx, vz, xx, zz, xz, lm, mu, b, tz, tr, head, items, end;
+  bool cached;  // the per-thread item records (resident.cuh) fit next to the tiles
   __host__ __device__ ResidentLayout(int ld, int r) : pitch(ld), rows(r) {
     int off = 16;  // slack
     vx = off; off += (r + 8) * ld + 16;
@@ -111,6 +113,9 @@ struct ResidentLayout {
     tz = off; off += ld;                      // Cerjan taper by column
     tr = off; off += ((r + 4 + 15) / 16) * 16;  // Cerjan taper by row, rows xs-2 .. xe+1
     head = off; off += ((r * (ld / 2) + 1) / 2 + 15) / 16 * 16;  // ints: first injection of each own pair
+    items = off;  // [threads] stress records of 3 doubles, then [threads] velocity records of 4 doubles
+    cached = (size_t)(off + 7 * kResidentThreads) * sizeof(double) <= kResidentSmemBudget;
+    if (cached) off += 7 * kResidentThreads;
     end = off;
   }
   __host__ __device__ size_t bytes() const { return (size_t)end * sizeof(double); }

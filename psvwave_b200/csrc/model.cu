@@ -1186,7 +1186,7 @@ bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t
   int r = resident_rows_ > 0 ? resident_rows_ : 2;
   for (;; ++r) {
     const size_t bytes = resident_smem_bytes(ld_, r);
-    if (bytes > kMaxDynamicSmem) return no("the strips do not fit in shared memory");
+    if (bytes > kResidentSmemBudget) return no("the strips do not fit in shared memory");
     auto f = resident_capacity_.find(r);
     if (f == resident_capacity_.end()) f = resident_capacity_.emplace(r, resident_max_ctas(bytes)).first;
     const int need = (cfg_.nx + r - 1) / r;

@@ -248,9 +248,9 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     return it;
   };
   struct VelItem {
-    int i, v, s, pk;  // own-pair index, velocity- and stress-tile index, packet offset inside a parity buffer
-    unsigned flags;   // 1 update, 2 lower column, 4 upper column, 8 field is vz, 16 row is read by a neighbour, 32 upper
-                      // column inside the grid
+    int i, pk;       // own-pair index (velocity tile: i + 4 P2, stress tile: i + 2 P2), packet offset in a parity buffer
+    unsigned flags;  // 1 update, 2 lower column, 4 upper column, 8 field is vz, 16 row is read by a neighbour, 32 upper
+    int pad;         // column inside the grid
     double tpa, tpb;
   };
   auto vel_item = [&](int w) {
@@ -261,8 +261,7 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     const bool rowok = gx0 + x >= 2 && gx0 + x < gnx - 2;
     const bool za = z0 >= 2 && z0 < nz - 2, zb = z0 + 1 >= 2 && z0 + 1 < nz - 2;
     it.i = i;
-    it.v = (jr + 4) * P2 + kp;
-    it.s = (jr + 2) * P2 + kp;
+    it.pad = 0;
     it.pk = (int)(fz * field_packets) + x * ld + z0;
     it.flags = (rowok && (za || zb) ? 1u : 0u) | (za ? 2u : 0u) | (zb ? 4u : 0u) | (fz ? 8u : 0u) |
                ((jr < 3 || jr >= own - 3) && z0 < nz ? 16u : 0u) | (z0 + 1 < nz ? 32u : 0u);
@@ -272,10 +271,15 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     return it;
   };
   const int n_stress = (own + 4) * P2, n_vel = 2 * own * P2;
-  StressItem s_first{0, 0u, 0.0, 0.0};
-  VelItem v_first{0, 0, 0, 0, 0u, 0.0, 0.0};
-  if (tid < n_stress) s_first = stress_item(tid);
-  if (tid < n_vel) v_first = vel_item(tid);
+  // one record per thread and phase in shared memory when they fit next to the tiles (in registers they spill;
+  // same-box A/B: profiles/r2c_resident_kernel.md), else every step works them out again
+  const bool cached = L.cached;
+  StressItem *s_first = reinterpret_cast<StressItem *>(sm + L.items);
+  VelItem *v_firsts = reinterpret_cast<VelItem *>(sm + L.items + 3 * kResidentThreads);
+  if (cached) {
+    if (tid < n_stress) s_first[tid] = stress_item(tid);
+    if (tid < n_vel) v_firsts[tid] = vel_item(tid);
+  }
   side_effects(fwd ? 0 : a.nsteps - 1);
 
   for (int step = 0; step < a.nsteps; ++step) {
@@ -324,7 +328,7 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
     // 2. the stress components the own velocities read, in place: txx rows [xs-2, xe], tzz own rows, txz rows
     //    [xs-1, xe+1]
     for (int i = tid; i < n_stress; i += nthreads) {
-      const StressItem it = i == tid ? s_first : stress_item(i);
+      const StressItem it = cached && i == tid ? s_first[tid] : stress_item(i);
       if (!(it.flags & 1u)) continue;  // frame rows / pad pairs keep their values
       const bool za = it.flags & 2u, zb = it.flags & 4u;
       const bool do_xx = it.flags & 8u, do_zz = it.flags & 16u, do_xz = it.flags & 32u;
@@ -378,14 +382,14 @@ __global__ void __launch_bounds__(kResidentThreads, 1) resident_loop_kernel(cons
       // one (z-pair, field) per thread -- all vx pairs first, then all vz pairs, so a warp never holds both: the two
       // fields read disjoint stencil inputs, and twice as many warps share this latency-bound phase
       for (int w = tid; w < n_vel; w += nthreads) {
-        const VelItem it = w == tid ? v_first : vel_item(w);
-        const int i = it.i, v = it.v;
+        const VelItem it = cached && w == tid ? v_firsts[tid] : vel_item(w);
+        const int i = it.i, v = i + 4 * P2;
         const bool fz = it.flags & 8u, za = it.flags & 2u, zb = it.flags & 4u;
         double2 *tile = fz ? tvz : tvx;
         double2 val = tile[v];
         const double2 b = tb[i];
         if (it.flags & 1u) {
-          const int s = it.s;  // stress-tile index of (x, kp)
+          const int s = i + 2 * P2;  // stress-tile index of (x, kp)
           const double tpa = it.tpa, tpb = it.tpb;
           if (!fz) {  // vx: D-x txx + D-z txz
             const double2 xx_m2 = txx[s - 2 * P2], xx_m1 = txx[s - P2], xx_0 = txx[s], xx_p1 = txx[s + P2];
