@@ -324,7 +324,7 @@ def extra_slab_split(n_gpus: int, nt: int = 200) -> dict:
             "timing": "host clock around both marches, every stream synchronised on both sides, best of 2"}
 
 
-def extra_one_object(n_gpus: int, nt: int = 1000) -> dict:
+def extra_one_object(n_gpus: int, nt: int = 2000) -> dict:
     """psv_set_devices: ONE fdModel object over n_gpus devices, the reference's own user loop from a plain
     single-process script (no torchrun, no PyTorch): one shot per GPU of the headline workload's geometry."""
     import psvwave_b200
