@@ -298,6 +298,13 @@ int psv_stream(psv_handle h, void **stream);
 int psv_timer_start(psv_handle h);
 int psv_timer_stop(psv_handle h, double *milliseconds);
 
+/* Page-locked host memory for callers that want the library's copies to run at full PCIe / C2C speed (the shipped
+ * binding backs the large arrays its getters return with such buffers and recycles them): plain cudaHostAlloc /
+ * cudaFreeHost, no handle needed.  psv_host_alloc fails with PSV_ERR_CUDA / PSV_ERR_LENGTH when the memory cannot be
+ * pinned; any host pointer is accepted by every getter and setter. */
+int psv_host_alloc(size_t bytes, void **host_ptr);
+int psv_host_free(void *host_ptr);
+
 /* Tuning / instrumentation knobs, by name.  Unknown names fail with PSV_ERR_INVALID_ARGUMENT.
  *   "variant"  which step kernels run the time loop (results are the same):
  *              0 one thread per point, two sweeps      1 x-marching two sweeps

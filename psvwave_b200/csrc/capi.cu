@@ -686,6 +686,24 @@ int psv_timer_start(psv_handle h) {
 int psv_timer_stop(psv_handle h, double *milliseconds) {
   return guarded([&] { *milliseconds = group(h) ? h->g->timer_stop() : model(h).timer_stop(); });
 }
+int psv_host_alloc(size_t bytes, void **host_ptr) {
+  return guarded([&] {
+    if (!host_ptr) throw psv::invalid_argument("Null argument.");
+    *host_ptr = nullptr;
+    if (bytes == 0) return;
+    const cudaError_t e = cudaHostAlloc(host_ptr, bytes, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      *host_ptr = nullptr;
+      throw psv::cuda_error(std::string("cudaHostAlloc: ") + cudaGetErrorString(e));
+    }
+  });
+}
+int psv_host_free(void *host_ptr) {
+  return guarded([&] {
+    if (host_ptr) PSV_CUDA(cudaFreeHost(host_ptr));
+  });
+}
 int psv_set_option(psv_handle h, const char *name, long long value) {
   return guarded([&] {
     if (psv::DeviceGroup *g = group(h)) g->set_option(name, value);
