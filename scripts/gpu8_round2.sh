@@ -1,6 +1,6 @@
 #!/bin/bash
 # Everything round 2 wants measured on the 8-GPU box, in one gpurun --gpus 8 call (charged 8x: keep it short).
-OUT=gpurun_out/r2k
+OUT=gpurun_out/r2y
 mkdir -p $OUT
 cd "$(dirname "$0")/.."
 nvidia-smi -L | wc -l > $OUT/gpus.txt
@@ -17,7 +17,7 @@ tail -1 $OUT/bench_n8.json | cut -c1-300
 python - <<'PY'
 import json
 try:
-    d = json.loads(open("gpurun_out/r2k/bench_n8.json").read().strip().splitlines()[-1])
+    d = json.loads(open("gpurun_out/r2y/bench_n8.json").read().strip().splitlines()[-1])
     print("N=8 value", d["value"] / 1e9, "e2e", d["e2e"]["value"] / 1e9, json.dumps(d.get("extra"))[:900])
 except Exception as e:
     print("bench n8 parse failed", e)
