@@ -249,6 +249,9 @@ int psv_gradient_descent(psv_handle h, int iterations, double step_length, int r
  * after every iteration.  Not bit-comparable with SciPy's L-BFGS-B (another line search); the tests compare the misfit
  * reached on the notebook-2 problem. */
 int psv_get_gradient_vector_smoothed(psv_handle h, double sigma, double *out, size_t n);
+/* Host only (no device needed): the 2 * radius + 1 filter weights psv_get_gradient_vector_smoothed uses for `sigma` --
+ * scipy.ndimage's _gaussian_kernel1d(sigma, 0, int(4 sigma + 0.5)) -- written to weights_out (capacity doubles). */
+int psv_gaussian_weights(double sigma, double *weights_out, size_t capacity, int *radius_out);
 int psv_lbfgs(psv_handle h, int max_iterations, int history, double gtol, double smoothing_sigma,
               int release_each_shot, double *misfits_out, int *iterations_done, int *evaluations_done);
 /* Monte-Carlo ensembles (SURVEY 8e "replicas only"; the reference's route is n independent copies of

@@ -561,6 +561,18 @@ int psv_get_gradient_vector_smoothed(psv_handle h, double sigma, double *out, si
     else model(h).get_gradient_vector_smoothed(out, n, sigma);
   });
 }
+int psv_gaussian_weights(double sigma, double *weights_out, size_t capacity, int *radius_out) {
+  return guarded([&] {
+    if (!(sigma > 0.0)) throw psv::invalid_argument("Smoothing sigma must be > 0.");
+    int radius = 0;
+    const std::vector<double> w = psv::gaussian_weights(sigma, &radius);
+    if (radius_out) *radius_out = radius;
+    if (weights_out) {
+      if (capacity < w.size()) throw psv::length_error("psv_gaussian_weights: capacity too small.");
+      std::copy(w.begin(), w.end(), weights_out);
+    }
+  });
+}
 int psv_lbfgs(psv_handle h, int max_iterations, int history, double gtol, double smoothing_sigma,
               int release_each_shot, double *misfits_out, int *iterations_done, int *evaluations_done) {
   return guarded([&] {

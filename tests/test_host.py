@@ -181,3 +181,25 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in text.lower() or f == "parallel.py" and False, os.path.join(dirpath, f)
+
+
+@pytest.mark.parametrize("sigma", [0.5, 0.7, 1.0, 2.0, 2.5, 4.0, 7.3])
+def test_gaussian_weights_are_scipys(lib, sigma):
+    """The filter weights of psv_get_gradient_vector_smoothed (host code, no device): scipy.ndimage's
+    _gaussian_kernel1d(sigma, 0, int(4 sigma + 0.5)), the kernel behind gaussian_filter(..., sigma) that the
+    reference's _fwi class applies to the gradient (docs-source/source/typical-workflow.rst:61-69)."""
+    import numpy as np
+    from scipy.ndimage import _filters
+    radius = C.c_int(0)
+    buf = (C.c_double * 4096)()
+    lib.psv_gaussian_weights.argtypes = [C.c_double, C.POINTER(C.c_double), C.c_size_t,
+                                         C.POINTER(C.c_int)]
+    assert lib.psv_gaussian_weights(sigma, buf, 4096, C.byref(radius)) == 0
+    lw = int(4.0 * sigma + 0.5)
+    assert radius.value == lw
+    want = _filters._gaussian_kernel1d(sigma, 0, lw)
+    got = np.array(buf[:2 * lw + 1])
+    assert np.allclose(got, want, rtol=4e-16, atol=0)  # libm exp vs numpy's SIMD exp: at most an ulp or two
+    assert abs(got.sum() - 1.0) <= 4e-16
+    assert lib.psv_gaussian_weights(-1.0, buf, 4096, C.byref(radius)) != 0
+    assert lib.psv_gaussian_weights(sigma, buf, 1, C.byref(radius)) != 0  # capacity too small
