@@ -431,6 +431,7 @@ Model::Model(const Model &o, int device, bool with_snapshots) : cfg_(o.cfg_), de
   if (with_snapshots)
     for (int s = 0; s < cfg_.n_shots; ++s) dcopy(o.snapshots_[s], snapshots_[s]);
   build_plans();
+  if (l2_persist_mb_ > 0) apply_l2_window();  // a stream attribute: not inherited from the source's stream
   PSV_CUDA(cudaDeviceSynchronize());
   } catch (...) {  // the destructor does not run for a half-built object
     destroy_stream_and_events();
