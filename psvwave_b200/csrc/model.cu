@@ -1096,7 +1096,6 @@ void Model::launch_fused(double sdt, int mode, int point_mode, int i_shot, int s
   const FusedModel *models = fused_model_.as<FusedModel>();
   const int batch = 1 + (int)batch_followers_.size();
   if (fp32_) {
-    if (slab_) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
     if (variant_ == 3) {  // the march fed by the TMA ring, geometry like the FP64 default (option, measured, or formula)
       int tiles = 0, strip = 0;
       size_t smem64 = 0;
@@ -1757,23 +1756,24 @@ void Model::march_end() {
 }
 
 namespace {
-// rows [row0, row0 + rows) of the 5 state arrays <-> one contiguous staging block per side
+// rows [row0, row0 + rows) of the 5 state arrays <-> one contiguous staging block per side.  Everything in BYTES
+// (multiples of 16): the state is double, or float in the FP32 wavefield mode.
 struct HaloArgs {
-  double *state;  // vx of the current buffer; field k at + k * field_stride
+  char *state;  // vx of the current buffer; field k at + k * field_stride
   size_t field_stride;
-  double *staging;  // [side][field][chunk]
-  size_t chunk;     // rows * ld
-  size_t row_off[2];  // first element of the rows of side 0 / 1 inside a field
+  char *staging;  // [side][field][chunk]
+  size_t chunk;   // rows * ld * sizeof(element)
+  size_t row_off[2];  // first byte of the rows of side 0 / 1 inside a field
   int active[2];
 };
 template <bool PACK>
 __global__ void halo_copy_kernel(const HaloArgs a) {
   const int side = blockIdx.y / 5, field = blockIdx.y % 5;
   if (!a.active[side]) return;
-  double2 *grid = reinterpret_cast<double2 *>(a.state + field * a.field_stride + a.row_off[side]);
-  double2 *stage = reinterpret_cast<double2 *>(a.staging + ((size_t)side * 5 + field) * a.chunk);
-  const size_t n2 = a.chunk >> 1;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) {
+  int4 *grid = reinterpret_cast<int4 *>(a.state + field * a.field_stride + a.row_off[side]);
+  int4 *stage = reinterpret_cast<int4 *>(a.staging + ((size_t)side * 5 + field) * a.chunk);
+  const size_t n = a.chunk >> 4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     if (PACK) stage[i] = grid[i];
     else grid[i] = stage[i];
   }
@@ -1785,8 +1785,10 @@ void Model::halo_pack() {
   bind();
   const int H = std::max(halo_lo_, halo_hi_);
   if (H == 0) return;
-  HaloArgs a{F(0), field_stride_, halo_send_.as<>(), (size_t)H * ld_,
-             {(size_t)halo_lo_ * ld_, (size_t)(cfg_.nx - halo_hi_ - H) * ld_}, {halo_lo_ > 0, halo_hi_ > 0}};
+  const size_t es = fp32_ ? sizeof(float) : sizeof(double);
+  char *state = fp32_ ? reinterpret_cast<char *>(field32_ptr(cur_, 0)) : reinterpret_cast<char *>(F(0));
+  HaloArgs a{state, field_stride_ * es, halo_send_.as<char>(), (size_t)H * ld_ * es,
+             {(size_t)halo_lo_ * ld_ * es, (size_t)(cfg_.nx - halo_hi_ - H) * ld_ * es}, {halo_lo_ > 0, halo_hi_ > 0}};
   halo_copy_kernel<true><<<dim3(64, 10), 256, 0, stream_>>>(a);
   PSV_CUDA(cudaGetLastError());
   ++stat_launches_;
@@ -1797,8 +1799,10 @@ void Model::halo_unpack() {
   bind();
   const int H = std::max(halo_lo_, halo_hi_);
   if (H == 0) return;
-  HaloArgs a{F(0), field_stride_, halo_recv_.as<>(), (size_t)H * ld_,
-             {(size_t)0, (size_t)(cfg_.nx - H) * ld_}, {halo_lo_ > 0, halo_hi_ > 0}};
+  const size_t es = fp32_ ? sizeof(float) : sizeof(double);
+  char *state = fp32_ ? reinterpret_cast<char *>(field32_ptr(cur_, 0)) : reinterpret_cast<char *>(F(0));
+  HaloArgs a{state, field_stride_ * es, halo_recv_.as<char>(), (size_t)H * ld_ * es,
+             {(size_t)0, (size_t)(cfg_.nx - H) * ld_ * es}, {halo_lo_ > 0, halo_hi_ > 0}};
   halo_copy_kernel<false><<<dim3(64, 10), 256, 0, stream_>>>(a);
   PSV_CUDA(cudaGetLastError());
   ++stat_launches_;
@@ -1806,21 +1810,21 @@ void Model::halo_unpack() {
 
 // ---- the slabs of one process exchange halos peer to peer ----
 namespace {
-struct PullArgs {
-  double *dst;         // my vx (current buffer); field k at + k * field_stride
+struct PullArgs {  // bytes throughout (the state is double, or float in the FP32 wavefield mode)
+  char *dst;         // my vx (current buffer); field k at + k * dst_stride
   size_t dst_stride;
-  const double *src[2];  // the neighbour's vx (current buffer) per side, or null
+  const char *src[2];  // the neighbour's vx (current buffer) per side, or null
   size_t src_stride[2];
-  size_t dst_off[2], src_off[2];  // first element of the H rows inside a field
-  size_t chunk;                   // H * ld
+  size_t dst_off[2], src_off[2];  // first byte of the H rows inside a field
+  size_t chunk;                   // H * ld * sizeof(element)
 };
 __global__ void halo_pull_kernel(const PullArgs a) {
   const int side = blockIdx.y / 5, field = blockIdx.y % 5;
   if (!a.src[side]) return;
-  const double2 *src = reinterpret_cast<const double2 *>(a.src[side] + field * a.src_stride[side] + a.src_off[side]);
-  double2 *dst = reinterpret_cast<double2 *>(a.dst + field * a.dst_stride + a.dst_off[side]);
-  const size_t n2 = a.chunk >> 1;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x)
+  const int4 *src = reinterpret_cast<const int4 *>(a.src[side] + field * a.src_stride[side] + a.src_off[side]);
+  int4 *dst = reinterpret_cast<int4 *>(a.dst + field * a.dst_stride + a.dst_off[side]);
+  const size_t n = a.chunk >> 4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dst[i] = src[i];  // loads cross NVLink when the neighbour lives on another GPU (peer access)
 }
 }  // namespace
@@ -1847,14 +1851,20 @@ void Model::pull_halos(const Model *lower, const Model *upper) {
     }
   slab_peer_checked_ = true;
   // my rows [0, H) <- the lower neighbour's last H owned rows; my rows [nx-H, nx) <- the upper one's first H owned rows
-  const size_t chunk = (size_t)H * ld_;
-  const size_t dst_off[2] = {0, (size_t)(cfg_.nx - H) * ld_};
+  const size_t es = fp32_ ? sizeof(float) : sizeof(double);
+  auto state = [es](const Model *m) {
+    return m->fp32_ ? reinterpret_cast<char *>(m->field32_ptr(m->cur_, 0)) : reinterpret_cast<char *>(m->F(0));
+  };
+  for (const Model *o : nb)
+    if (o && o->fp32_ != fp32_) throw state_error("The slabs of one grid must agree on the FP32 wavefield mode.");
+  const size_t chunk = (size_t)H * ld_ * es;
+  const size_t dst_off[2] = {0, (size_t)(cfg_.nx - H) * ld_ * es};
   size_t src_off[2] = {0, 0};
-  if (nb[0]) src_off[0] = (size_t)(nb[0]->cfg_.nx - nb[0]->halo_hi_ - H) * ld_;
-  if (nb[1]) src_off[1] = (size_t)nb[1]->halo_lo_ * ld_;
+  if (nb[0]) src_off[0] = (size_t)(nb[0]->cfg_.nx - nb[0]->halo_hi_ - H) * ld_ * es;
+  if (nb[1]) src_off[1] = (size_t)nb[1]->halo_lo_ * ld_ * es;
   if (direct) {
-    PullArgs a{F(0), field_stride_, {nb[0] ? nb[0]->F(0) : nullptr, nb[1] ? nb[1]->F(0) : nullptr},
-               {nb[0] ? nb[0]->field_stride_ : 0, nb[1] ? nb[1]->field_stride_ : 0},
+    PullArgs a{state(this), field_stride_ * es, {nb[0] ? state(nb[0]) : nullptr, nb[1] ? state(nb[1]) : nullptr},
+               {nb[0] ? nb[0]->field_stride_ * es : 0, nb[1] ? nb[1]->field_stride_ * es : 0},
                {dst_off[0], dst_off[1]}, {src_off[0], src_off[1]}, chunk};
     halo_pull_kernel<<<dim3(32, 10), 256, 0, stream_>>>(a);
     PSV_CUDA(cudaGetLastError());
@@ -1864,8 +1874,9 @@ void Model::pull_halos(const Model *lower, const Model *upper) {
   for (int side = 0; side < 2; ++side)  // no peer mapping between the two GPUs: the copy engine routes it
     if (nb[side])
       for (int k = 0; k < 5; ++k)
-        PSV_CUDA(cudaMemcpyPeerAsync(F(k) + dst_off[side], device_, nb[side]->F(k) + src_off[side], nb[side]->device_,
-                                     chunk * sizeof(double), stream_));
+        PSV_CUDA(cudaMemcpyPeerAsync(state(this) + k * field_stride_ * es + dst_off[side], device_,
+                                     state(nb[side]) + k * nb[side]->field_stride_ * es + src_off[side],
+                                     nb[side]->device_, chunk, stream_));
 }
 
 void Model::march_slabs(Model *const *slabs, int n, int i_shot, bool adjoint, bool store_fields) {
@@ -1934,12 +1945,13 @@ void Model::march_slabs(Model *const *slabs, int n, int i_shot, bool adjoint, bo
 }
 
 void Model::halo_buffers(void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) const {
-  const size_t side = 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_;
-  *send_lo = halo_lo_ ? halo_send_.as<>() : nullptr;
-  *send_hi = halo_hi_ ? halo_send_.as<>() + side : nullptr;
-  *recv_lo = halo_lo_ ? halo_recv_.as<>() : nullptr;
-  *recv_hi = halo_hi_ ? halo_recv_.as<>() + side : nullptr;
-  *count = side;
+  // one side = 5 fields x halo rows of the state's element type; `count` is its length in doubles
+  const size_t side_bytes = 5 * (size_t)std::max(halo_lo_, halo_hi_) * ld_ * (fp32_ ? sizeof(float) : sizeof(double));
+  *send_lo = halo_lo_ ? halo_send_.as<char>() : nullptr;
+  *send_hi = halo_hi_ ? halo_send_.as<char>() + side_bytes : nullptr;
+  *recv_lo = halo_lo_ ? halo_recv_.as<char>() : nullptr;
+  *recv_hi = halo_hi_ ? halo_recv_.as<char>() + side_bytes : nullptr;
+  *count = side_bytes / sizeof(double);
 }
 
 void Model::slab_info(long long out[7]) const {
@@ -2657,7 +2669,6 @@ void Model::set_option(const std::string &name, long long v) {
     fused_strip_ = (int)v;
   } else if (name == "fp32") {
     bind();
-    if (slab_ && v) throw invalid_argument("The FP32 wavefield mode is not available on a slab of a split grid.");
     if ((v != 0) != fp32_) {
       PSV_CUDA(cudaStreamSynchronize(stream_));
       for (DeviceBuffer &sn : snapshots_) sn.release();  // the element size of the snapshots changes

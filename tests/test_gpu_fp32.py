@@ -87,9 +87,6 @@ def test_fp32_refuses_what_it_does_not_cover(tmp_path):
     m = fd(ini, fp32=1, variant=1)
     with pytest.raises(ValueError):
         m.forward_simulate(0)
-    s = psvwave_b200.fdModel._slab(ini, 0, 2, 8)
-    with pytest.raises(ValueError):
-        s._set_option("fp32", 1)
     a, b = fd(ini, fp32=1), fd(ini)
     with pytest.raises(ValueError):
         psvwave_b200.forward_batch([a, b], 0, False)
@@ -98,3 +95,25 @@ def test_fp32_refuses_what_it_does_not_cover(tmp_path):
     c = fd(ini, fp32=1)
     c.forward_simulate(0, True)
     assert np.array_equal(a.get_synthetic_data()[0][0], c.get_synthetic_data()[0][0])
+
+
+@pytest.mark.parametrize("n_slabs,native", [(2, True), (3, True), (2, False)])
+def test_fp32_on_a_split_grid_equals_the_whole_grid(golden, n_slabs, native):
+    """The FP32 mode on x-slabs (halo rows travel as floats): same kernels, same arithmetic on the same inputs, so the
+    split run is bit-identical to the whole-grid FP32 run -- and within the stated tolerance of the FP64 reference."""
+    import psvwave_b200
+    g = golden("small_multishot")
+    devices = list(range(min(psvwave_b200.device_count(), n_slabs))) if native else None
+    d = psvwave_b200.SlabDomain(SMALL_INI, n_slabs=n_slabs, halo_steps=2, options=dict(fp32=1), native=native,
+                                devices=devices)
+    w = fd(SMALL_INI, fp32=1)
+    for x in (d, w):
+        x.set_parameter_fields(g["vp"], g["vs"], g["rho"])
+        x.set_observed_data(g["obs_ux"], g["obs_uz"])
+        gradient_workflow(x)
+    assert np.array_equal(d.get_synthetic_data()[0], w.get_synthetic_data()[0])
+    assert np.array_equal(d.get_synthetic_data()[1], w.get_synthetic_data()[1])
+    for a, b in zip(d.get_kernels(), w.get_kernels()):
+        assert np.array_equal(a, b)
+    assert np.array_equal(d.get_gradient_vector(), w.get_gradient_vector())
+    assert rel_l2(d.get_gradient_vector(), g["gradient"]) <= TOL32
