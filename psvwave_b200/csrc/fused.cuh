@@ -70,7 +70,7 @@ struct MarchWindow {
   double2 vz_m2, vz_m1, vz_0;         // old vz rows j-2 .. j
 };
 
-// Window fill straight from the old state in global memory (variants 2 and 3, stage A of 5).
+// Window fill straight from the old state in global memory (variants 2 and 3, stage A of 4).
 __device__ __forceinline__ void window_from_global(const double *ovx, const double *ovz, long long r,
                                                    long long ld2n, MarchWindow &w) {
   w.vx_m2 = __ldg(reinterpret_cast<const double2 *>(ovx) + r - 2 * ld2n);
@@ -131,7 +131,7 @@ struct MarchRange {
   int it;        // time index of this stage's step (receiver sample / stf / adjoint-source column)
 };
 
-// Result sink of variants 2 and 3 (and of stage B of variant 5): the new state in global memory.
+// Result sink of variants 2 and 3 (and of stage B of variant 4): the new state in global memory.
 struct GlobalSink {
   double *nvx, *nvz, *nxx, *nzz, *nxz;
   int xs, xe;

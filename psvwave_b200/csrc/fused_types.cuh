@@ -37,11 +37,11 @@ struct FusedCommon {
   int parity;       // old state = f[parity], new state = f[parity ^ 1]
   int n_zwarps;     // ceil(ld/2 / 28)
   int strip;        // rows per warp
-  int tile_pairs;   // variant 5: z-pairs per CTA tile
+  int tile_pairs;   // variant 4: z-pairs per CTA tile
   int pdl;             // variant 3: launched with programmatic stream serialization (see fused_pipe_kernel)
   int rec_increments;  // 1: receiver samples are stored as increments, the running sum follows the time loop
   int l2_mode;      // variant 3: bit 0 = medium rows evict_last in L2, bit 1 = state rows evict_first
-  int it_step;      // variant 5: time index of the second step = it + it_step (+1 forward, -1 adjoint)
+  int it_step;      // variant 4: time index of the second step = it + it_step (+1 forward, -1 adjoint)
   size_t field_stride;  // doubles between consecutive state arrays: f[p][k] = f[0][0] + (5p+k)*field_stride
   // snapshots / kernel accumulation
   size_t snap_field_stride;  // n_snap_alloc * nx*ld

@@ -1,4 +1,4 @@
-// Variant 5: TWO time steps per launch (temporal blocking through shared memory).
+// Variant 4: TWO time steps per launch (temporal blocking through shared memory).
 //
 // The state of a P-SV step is 5 words per point and a step is HBM-bound, so the cheapest byte
 // is the one never written: a CTA runs step t -> t+1 and step t+1 -> t+2 back to back on the
