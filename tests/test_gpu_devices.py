@@ -181,3 +181,35 @@ def test_environment_variable_spreads_unchanged_scripts(golden, monkeypatch):
     m.set_observed_data(g["obs_ux"], g["obs_uz"])
     gradient_workflow(m)
     assert rel_l2(m.get_gradient_vector(), g["gradient"]) <= 1e-10
+
+
+def test_group_run_model_and_receiver_files(golden, tmp_path, monkeypatch):
+    """fdModel::run_model (src/fdModel.cpp:1291-1308) and the receiver files (:971-1006, :1053-1126) on an object that
+    spans devices: same misfit / gradient / files as on one device; loaded observed data reach every replica."""
+    import psvwave_b200
+    from oracle.oracle import config_from_ini, write_ini
+    g = golden("small_multishot")
+    monkeypatch.chdir(tmp_path)
+    files = {}
+    results = []
+    for tag, devices in (("one", None), ("grp", [0, 0, 0])):
+        folder = tmp_path / tag
+        folder.mkdir()
+        ini = str(tmp_path / f"{tag}.ini")
+        write_ini(ini, dict(config_from_ini(SMALL_INI), observed_data_folder=str(folder), stf_folder=str(folder)))
+        m = prepare(ini, (g["vp"], g["vs"], g["rho"]), (g["obs_ux"], g["obs_uz"]), devices=devices, exact=1)
+        m.run_model(False, True)
+        results.append((m.misfit, m.get_gradient_vector()))
+        m.write_receivers()
+        files[tag] = {p.name: p.read_bytes() for p in sorted(folder.iterdir())}
+        # observed := the synthetics just written; the misfit of the same synthetics must then vanish on every replica
+        m.load_receivers(False)
+        for s in range(m.n_shots):
+            m.forward_simulate(s, False)
+        assert m.calculate_l2_misfit_shot(m.n_shots - 1) <= 1e-20 * results[-1][0]
+        m.calculate_l2_misfit()
+        assert m.misfit <= 1e-20 * results[-1][0]
+    assert files["one"].keys() == files["grp"].keys() and len(files["one"]) >= 2
+    assert files["one"] == files["grp"]
+    assert results[0][0] == results[1][0]
+    assert rel_l2(results[1][1], results[0][1]) <= 1e-13
