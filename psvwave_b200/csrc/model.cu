@@ -2,6 +2,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <mutex>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -921,11 +922,30 @@ void Model::pipe_geometry(int batch, int *tiles, int *strip, size_t *smem) {
 // Results do not depend on the geometry (same arithmetic per point), and the caller zeroes the state afterwards.
 // The candidates run with the point operations of the loop that follows (receiver samples / injections at time index
 // 0, which that loop writes again): the warp that carries them is the critical path of its CTA row.
+namespace {
+std::mutex g_tune_mutex;
+std::map<std::vector<long long>, std::pair<int, int>> g_tune_cache;  // shape key -> (consumer warps, strip rows)
+}  // namespace
+
 void Model::tune_pipe_geometry(int i_shot, int point_mode) {
   const int batch = 1 + (int)batch_followers_.size();
   if (variant_ != 3 || tune_ == 0 || pipe_warps_ != 0 || fused_strip_ != 0) return;
   if (tune_ < 0 && (long long)cfg_.nx * cfg_.nz * batch < (1ll << 21)) return;  // small grids: latency rules, see above
   if (tuned_strip_ > 0 && tuned_batch_ == batch) return;
+  // measured once per process for this device and problem shape: fresh objects of a Monte-Carlo run, the replicas of
+  // a device group and the slabs of equal shape reuse it
+  const std::vector<long long> key = {device_, cfg_.nx, cfg_.nz, ld_, batch, fp32_, exact_, pipe_stages_, l2_mode_,
+                                      slab_ ? x_off_ : -1, nx_global_, point_mode};
+  {
+    std::lock_guard<std::mutex> lock(g_tune_mutex);
+    auto f = g_tune_cache.find(key);
+    if (f != g_tune_cache.end() && tune_ < 1) {
+      tuned_warps_ = f->second.first;
+      tuned_strip_ = f->second.second;
+      tuned_batch_ = batch;
+      return;
+    }
+  }
   bind();
   const auto wall0 = std::chrono::steady_clock::now();
   int sms = 0;
@@ -996,6 +1016,10 @@ void Model::tune_pipe_geometry(int i_shot, int point_mode) {
   tuned_warps_ = best_w;
   tuned_strip_ = best_s;
   tuned_batch_ = batch;
+  {
+    std::lock_guard<std::mutex> lock(g_tune_mutex);
+    g_tune_cache[key] = {best_w, best_s};
+  }
   cur_ = cur0;
   // the caller zeroes THIS model's state next; the other members of an ensemble were zeroed before it was called
   PSV_CUDA(cudaStreamSynchronize(stream_));
