@@ -142,3 +142,27 @@ def test_slab_handles_refuse_what_needs_the_whole_grid(case):
     s._set_option("variant", 1)
     with pytest.raises(ValueError):
         s._march_begin(0, False, False)
+
+
+def test_march_slabs_checks_what_it_is_given(case):
+    """psv_march_slabs wants ALL slabs of one grid, in slab order, with one halo width and one arithmetic mode."""
+    import psvwave_b200
+    mk = lambda r, n, h: psvwave_b200.fdModel._slab(case["ini"], r, n, h)  # noqa: E731
+    a, b, c = mk(0, 3, 8), mk(1, 3, 8), mk(2, 3, 8)
+    with pytest.raises(ValueError):
+        psvwave_b200.march_slabs([b, a, c], 0, False, False)  # wrong order
+    with pytest.raises(ValueError):
+        psvwave_b200.march_slabs([a, b], 0, False, False)  # one slab missing
+    with pytest.raises(ValueError):
+        psvwave_b200.march_slabs([a, mk(1, 3, 16), c], 0, False, False)  # another halo width
+    with pytest.raises(RuntimeError):
+        psvwave_b200.march_slabs([psvwave_b200.fdModel(case["ini"])], 0, False, False)  # not a slab
+    b._set_option("fp32", 1)
+    with pytest.raises(RuntimeError):
+        psvwave_b200.march_slabs([a, b, c], 0, False, False)  # the slabs must agree on the FP32 mode
+    b._set_option("fp32", 0)
+    psvwave_b200.march_slabs([a, b, c], 0, False, False)  # and no failed attempt leaves a march open
+    with pytest.raises(RuntimeError):
+        psvwave_b200.march_slabs([a, b, c], 0, True, False)  # adjoint without a stored forward march
+    psvwave_b200.march_slabs([a, b, c], 0, False, True)
+    psvwave_b200.march_slabs([a, b, c], 0, True, False)
