@@ -308,6 +308,29 @@ int psv_timer_stop(psv_handle h, double *milliseconds);
 int psv_host_alloc(size_t bytes, void **host_ptr);
 int psv_host_free(void *host_ptr);
 
+/* The L2 misfit of psv_calculate_l2_misfit, computed without allocating anything.  NO COUNTERPART IN THE REFERENCE:
+ * it exists for callers that may not reach cudaMalloc -- a host program that gave all GPU memory to its own arena
+ * and forbids plug-ins to ask the driver for more, or a sampling loop that cannot afford the device-wide stall every
+ * cudaMalloc / cudaFree brings.  Everything is DEVICE memory owned by the caller: the four seismogram arrays
+ * (synthetic ux, uz; observed ux, uz; n doubles each, any contiguous range in (shot, receiver, time) order) and the
+ * one double the result is written to.  The block partial sums, which the handle-based call keeps in a cudaMalloc'ed
+ * buffer, live in a fixed 64 KiB array inside the library image instead; each GPU that loads the library holds that
+ * array until the process ends.
+ *  - limit: n <= PSV_MISFIT_STATIC_MAX_SAMPLES per array, larger n fails with PSV_ERR_LENGTH and launches nothing
+ *    (sum several ranges yourself, or use the handle-based call);
+ *  - runs on the device that is current in the calling thread, ordered on `stream` (a cudaStream_t, NULL = default
+ *    stream); returns once the two kernels are enqueued, the result is valid after the stream reaches that point;
+ *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call before
+ *    any stream capture begins;
+ *  - the array is shared by every call on that GPU and keeps the previous call's values (harmless: each call writes
+ *    the slots it later reads); calls that overlap in time on one GPU race on it -- keep them on one stream;
+ *  - value: bit-identical to psv_calculate_l2_misfit / psv_calculate_l2_misfit_shot on the same arrays with
+ *    dt = PSV_REAL_DT (same terms 0.5*dt*d^2, same order of additions). */
+#define PSV_MISFIT_STATIC_MAX_SAMPLES 33554432 /* 8192 block partials x 4096 samples per block */
+int psv_l2_misfit_static_scratch(const double *device_ux, const double *device_uz, const double *device_obs_ux,
+                                 const double *device_obs_uz, size_t n, double dt, double *device_misfit_out,
+                                 void *stream);
+
 /* Tuning / instrumentation knobs, by name.  Unknown names fail with PSV_ERR_INVALID_ARGUMENT.
  *   "variant"  which step kernels run the time loop (results are the same):
  *              0 one thread per point, two sweeps      1 x-marching two sweeps

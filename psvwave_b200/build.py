@@ -31,7 +31,7 @@ HOST_CXX = "/usr/bin/g++"  # the image's $CXX wrapper (/opt/gcc) lacks a few spe
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 LIB_SOURCES = ["capi.cu", "model.cu", "multi.cu", "optim.cu", "config.cpp", "launch_step.cu", "launch_pipe.cu", "launch_pair.cu",
-               "launch_resident.cu"]
+               "launch_resident.cu", "no_alloc.cu"]
 
 
 def _includes(path: str, seen: set[str]) -> None:

@@ -730,3 +730,8 @@ int psv_get_stat(psv_handle h, const char *name, double *value) {
 }
 
 }  // extern "C"
+
+// Other translation units of the library (no_alloc.cu) report their failures through psv_last_error() too.
+namespace psv {
+void set_last_error(const char *message) { g_error = message ? message : ""; }
+}  // namespace psv
