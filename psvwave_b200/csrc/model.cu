@@ -1192,6 +1192,11 @@ namespace {
 constexpr long long kResidentAutoPoints = 1 << 18;
 }  // namespace
 
+// Threads per CTA of the loop kernel: one per pair of columns of the rows a strip updates (+ halo), at most the
+// compiled maximum.  resident.cuh gives each source / receiver of a strip to ONE thread, so this is also the number
+// of point operations a strip can hold.
+static int resident_threads(int ld, int rows) { return std::min(kResidentThreads, round_up((rows + 4) * (ld / 2), 32)); }
+
 // Rows per CTA, CTAs and shared memory of the loop kernel for this grid, or false when it does not apply.
 // `forced` (option "resident" = 1) turns the reasons into errors.
 bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t *smem) {
@@ -1223,12 +1228,15 @@ bool Model::resident_plan(int i_shot, bool adjoint, int *rows, int *ctas, size_t
     if (f->second == 0) return no("cooperative launch is not available");
     if (resident_rows_ > 0) return no("resident_rows: too many strips to be co-resident");
   }
-  // a strip's point operations are handled one per thread
+  // a strip's point operations are handled one per thread OF THE LAUNCH (narrow grids run fewer than
+  // kResidentThreads threads, see resident_threads): the limits are the launched count, not the compiled maximum
+  const int threads = resident_threads(ld_, *rows);
+  const int max_ops = std::min(threads, kResidentMaxOps);
   const std::vector<int> &ops = plans_[i_shot].op_row_start_host, &rec = rec_row_start_host_;
   for (int x = 0; x < cfg_.nx; x += *rows) {
     const int xe = std::min(x + *rows, cfg_.nx);
-    if ((!adjoint && (ops[xe] - ops[x] > kResidentMaxOps || rec[xe] - rec[x] > kResidentThreads)) ||
-        (adjoint && rec[xe] - rec[x] > kResidentMaxOps))
+    if ((!adjoint && (ops[xe] - ops[x] > max_ops || rec[xe] - rec[x] > threads)) ||
+        (adjoint && rec[xe] - rec[x] > max_ops))
       return no("too many sources / receivers in one strip");
   }
   return true;
@@ -1267,7 +1275,9 @@ void Model::run_resident(int i_shot, bool adjoint, bool store, int rows, int cta
     if (resident_timing_buf_.bytes() < tb) resident_timing_buf_.allocate(tb);
     a.timing = resident_timing_buf_.as<long long>();
   }
-  const int threads = std::min(kResidentThreads, round_up((rows + 4) * (ld_ / 2), 32));
+  const int threads = resident_threads(ld_, rows);
+  // a spin-limit abort of an earlier launch (debugger, time-slicing) must not fail every later call of this model
+  PSV_CUDA(cudaMemsetAsync(a.abort, 0, sizeof(unsigned), stream_));
   launch_resident(exact_, a, dim3(ctas, 1), threads, smem, stream_);
   cur_ = c.nt & 1;
   ++stat_launches_;

@@ -155,3 +155,47 @@ def test_what_the_loop_kernel_refuses(tmp_path):
     finally:
         os.chdir(cwd)
     assert m._get_stat("resident_ctas") == 0
+
+
+def test_narrow_grid_with_more_receivers_than_threads_in_a_strip(tmp_path):
+    """A narrow grid launches fewer threads per CTA than the compiled maximum (nz = 24 -> pitch 32 -> 96 threads for
+    2-row strips) and the loop kernel gives each receiver / source of a strip to one thread: 110 receivers on one grid
+    row do not fit.  The plan has to see that -- automatic mode falls back to the per-step kernels (same seismograms
+    and kernels as resident = 0, bit for bit), resident = 1 says why -- instead of dropping receivers 96..109.  90
+    receivers on that row do fit and run in the loop kernel, identical to the per-step result."""
+    import psvwave_b200
+
+    def run(nr, resident):
+        ini = str(tmp_path / f"narrow{nr}.ini")
+        ragged_config(ini, nt=120, nx_inner=40, nz_inner=10, nx_inner_boundary=3, nz_inner_boundary=2, n_sources=2,
+                      ix_sources=[12, 30], iz_sources=[4, 6], moment_angles=[20.0, 70.0], n_shots=1,
+                      which_source_to_fire_in_which_shot=[[0, 1]], nr=nr, ix_receivers=[9] * nr,
+                      iz_receivers=[k % 10 for k in range(nr)], npx=1, npz=1)
+        m = psvwave_b200.fdModel(ini)
+        m._set_option("exact", 1)
+        m._set_option("resident", resident)
+        vp, vs, rho = random_medium(m.nx, m.nz, seed=3)
+        m.set_parameter_fields(vp, vs, rho)
+        m.forward_simulate(0, True)
+        fwd_ctas = m._get_stat("resident_ctas")
+        ux, uz = m.get_synthetic_data()
+        m.set_observed_data(ux * 1.1, uz * 0.9)
+        gradient_workflow(m)
+        return m, fwd_ctas, m._get_stat("resident_ctas")
+
+    ref, c0, c1 = run(110, 0)
+    assert c0 == 0 and c1 == 0
+    auto, c0, c1 = run(110, -1)
+    assert c0 == 0 and c1 == 0  # too many point operations for 96 threads: per-step launches
+    few_ref, _, _ = run(90, 0)
+    few, c0, c1 = run(90, -1)
+    assert c0 >= 1 and c1 >= 1  # fits: the loop kernel runs
+    for a, b in ((auto, ref), (few, few_ref)):
+        ux, uz = a.get_synthetic_data()
+        rx, rz = b.get_synthetic_data()
+        assert np.all(np.abs(rx).max(axis=2) > 0)  # every trace recorded
+        assert np.array_equal(ux, rx) and np.array_equal(uz, rz)
+        for name in KERNELS:
+            close(gpu_array(a, name), gpu_array(b, name), name, True)
+    with pytest.raises(ValueError, match="too many sources / receivers"):
+        run(110, 1)
