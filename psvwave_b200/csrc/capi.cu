@@ -624,7 +624,10 @@ int psv_create_slab_from_ini(const char *ini_path, int rank, int nranks, int hal
   });
 }
 int psv_slab_info(psv_handle h, long long out[7]) {
-  return guarded([&] { model(h).slab_info(out); });
+  return guarded([&] {
+    single_device_only(h, "psv_slab_info");
+    model(h).slab_info(out);
+  });
 }
 int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields) {
   return guarded([&] {
@@ -634,12 +637,16 @@ int psv_march_begin(psv_handle h, int i_shot, int adjoint, int store_fields) {
 }
 int psv_march_steps(psv_handle h, int n, int *done) {
   return guarded([&] {
+    single_device_only(h, "The domain split (psv_march_*)");
     const int d = model(h).march_steps(n);
     if (done) *done = d;
   });
 }
 int psv_march_end(psv_handle h) {
-  return guarded([&] { model(h).march_end(); });
+  return guarded([&] {
+    single_device_only(h, "The domain split (psv_march_*)");
+    model(h).march_end();
+  });
 }
 int psv_march_slabs(const psv_handle *slabs, int n, int i_shot, int adjoint, int store_fields) {
   return guarded([&] {
@@ -653,20 +660,28 @@ int psv_march_slabs(const psv_handle *slabs, int n, int i_shot, int adjoint, int
   });
 }
 int psv_halo_pack(psv_handle h) {
-  return guarded([&] { model(h).halo_pack(); });
+  return guarded([&] {
+    single_device_only(h, "The halo exchange (psv_halo_*)");
+    model(h).halo_pack();
+  });
 }
 int psv_halo_unpack(psv_handle h) {
-  return guarded([&] { model(h).halo_unpack(); });
+  return guarded([&] {
+    single_device_only(h, "The halo exchange (psv_halo_*)");
+    model(h).halo_unpack();
+  });
 }
 int psv_halo_buffers(psv_handle h, void **send_lo, void **send_hi, void **recv_lo, void **recv_hi, size_t *count) {
   return guarded([&] {
     if (!send_lo || !send_hi || !recv_lo || !recv_hi || !count) throw psv::invalid_argument("Null argument.");
+    single_device_only(h, "The halo exchange (psv_halo_*)");
     model(h).halo_buffers(send_lo, send_hi, recv_lo, recv_hi, count);
   });
 }
 int psv_stream(psv_handle h, void **stream) {
   return guarded([&] {
     if (!stream) throw psv::invalid_argument("Null argument.");
+    if (psv::DeviceGroup *g = group(h)) g->synchronize();  // queued runs finish before the primary's stream is handed out
     *stream = (void *)model(h).stream();
   });
 }
@@ -723,7 +738,10 @@ int psv_set_option(psv_handle h, const char *name, long long value) {
   });
 }
 int psv_get_option(psv_handle h, const char *name, long long *value) {
-  return guarded([&] { *value = model(h).get_option(name); });
+  return guarded([&] {
+    if (psv::DeviceGroup *g = group(h)) g->synchronize();  // a queued run may still be choosing (tuner) what is read here
+    *value = model(h).get_option(name);
+  });
 }
 int psv_get_stat(psv_handle h, const char *name, double *value) {
   return guarded([&] { *value = group(h) ? h->g->get_stat(name) : model(h).get_stat(name); });

@@ -118,7 +118,7 @@ DeviceGroup::DeviceGroup(DeviceGroup &o, Model *primary_clone) : primary_(primar
   o.drain();
   for (auto &r : o.replicas_) replicas_.emplace_back(new Model(*r));
   syn_elsewhere_ = o.syn_elsewhere_;
-  kernels_spread_ = o.kernels_spread_;
+  kernels_spread_ = o.kernels_spread_.load();
   shared_device_ = o.shared_device_;
   last_run_ = o.last_run_;
   start_workers();
@@ -222,18 +222,26 @@ void DeviceGroup::forward_simulate(int i_shot, bool store_fields, bool verbose, 
   check_shot(i_shot);
   const int k = owner(i_shot);
   Model *m = &rep(k);
-  if (k != 0) syn_elsewhere_[i_shot] = 1;
   last_run_ = k;
-  post(k, [=] { m->forward_simulate(i_shot, store_fields, verbose, output_wavefields); });
+  // The book-keeping flags are raised by the task itself, after the run succeeded: a run that throws (or one that
+  // post() drops behind an earlier failure) must not make gather_synthetics() / reduce_kernels() pull rows a replica
+  // never computed over the primary's valid ones.  The caller reads the flags only after drain(), which takes the
+  // worker's mutex after the task finished.
+  post(k, [=] {
+    m->forward_simulate(i_shot, store_fields, verbose, output_wavefields);
+    if (k != 0) syn_elsewhere_[i_shot] = 1;  // one writer per shot: its owner's worker
+  });
 }
 
 void DeviceGroup::adjoint_simulate(int i_shot, bool verbose) {
   check_shot(i_shot);
   const int k = owner(i_shot);
   Model *m = &rep(k);
-  if (k != 0) kernels_spread_ = true;
   last_run_ = k;
-  post(k, [=] { m->adjoint_simulate(i_shot, verbose); });
+  post(k, [=] {
+    m->adjoint_simulate(i_shot, verbose);
+    if (k != 0) kernels_spread_ = true;
+  });
 }
 
 void DeviceGroup::gather_synthetics() {
@@ -343,16 +351,14 @@ double DeviceGroup::run_gradient(bool release_each_shot) {
   for (int s = 0; s < n_shots; ++s) {
     const int k = owner(s);
     Model *m = &rep(k);
-    if (k != 0) {
-      syn_elsewhere_[s] = 1;
-      kernels_spread_ = true;
-    }
     last_run_ = k;
     post(k, [=] {
       m->forward_simulate(s, true, false, false);
+      if (k != 0) syn_elsewhere_[s] = 1;
       (*per_shot)[s] = m->calculate_l2_misfit_shot(s);
       m->calculate_l2_adjoint_sources();
       m->adjoint_simulate(s, false);
+      if (k != 0) kernels_spread_ = true;
       if (release_each_shot) m->release_snapshots(s);
     });
   }

@@ -17,6 +17,7 @@
 //   * snapshots stay on the GPU that produced them.
 #pragma once
 
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <deque>
@@ -115,7 +116,7 @@ class DeviceGroup {
   std::vector<std::unique_ptr<Model>> replicas_;  // replicas 1..n-1
   std::vector<std::unique_ptr<Worker>> workers_;
   std::vector<char> syn_elsewhere_;  // per shot: the newest synthetics are on the owner, not yet on the primary
-  bool kernels_spread_ = false;      // a non-primary replica accumulated since the last all-reduce
+  std::atomic<bool> kernels_spread_{false};  // a non-primary replica accumulated since the last all-reduce (set by workers)
   int last_run_ = 0;                 // replica of the most recent simulate call (dynamic fields, counters)
   std::vector<void *> comms_;        // ncclComm_t per replica, created at the first all-reduce
   bool shared_device_ = false;       // test configuration: several replicas on one GPU (no NCCL)

@@ -146,6 +146,9 @@ def test_group_reports_failures_of_queued_calls_and_bad_arguments(golden):
     m.adjoint_simulate(1)  # no stored forward field: fails on the worker ...
     with pytest.raises(RuntimeError, match="forward"):
         m.synchronize()  # ... and is reported by the next call that waits
+    m.map_kernels_to_velocity()
+    assert m._get_stat("local_sums") == 0  # the failed run raised no "kernels are spread" flag: nothing to sum
+    assert m._get_option("exact") == 0  # option reads wait for queued runs on a group handle too
     gradient_workflow(m)  # the object stays usable
     assert rel_l2(m.get_gradient_vector(), g["gradient"]) <= 1e-10
     with pytest.raises(ValueError):
