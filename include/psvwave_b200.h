@@ -246,7 +246,9 @@ int psv_gradient_descent(psv_handle h, int iterations, double step_length, int r
  * condition -- every evaluation being psv_run_gradient (+ the smoothing when smoothing_sigma > 0).  Starts from the
  * object's current medium, stops after max_iterations or when max|g| <= gtol, leaves the final medium in the object.
  * misfits_out[0 .. *iterations_done] (capacity max_iterations + 1, may be NULL) receives the misfit before the first and
- * after every iteration.  Not bit-comparable with SciPy's L-BFGS-B (another line search); the tests compare the misfit
+ * after every iteration.  End state: medium, synthetics, sensitivity kernels and misfit all belong to the returned point
+ * (when the line search gives up, that point is evaluated once more; it counts in *evaluations_done).  Smoothing calls on
+ * one GPU are serialised inside the library (one set of filter weights per device).  Not bit-comparable with SciPy's L-BFGS-B (another line search); the tests compare the misfit
  * reached on the notebook-2 problem. */
 int psv_get_gradient_vector_smoothed(psv_handle h, double sigma, double *out, size_t n);
 /* Host only (no device needed): the 2 * radius + 1 filter weights psv_get_gradient_vector_smoothed uses for `sigma` --

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <mutex>
 #include <stdexcept>
 
 #include "model.hpp"
@@ -112,12 +113,21 @@ __global__ void step_kernel(const double *__restrict__ x, double alpha, const do
 unsigned blocks(size_t n, int per) { return (unsigned)std::max<size_t>(1, (n + per - 1) / per); }
 }  // namespace
 
+constexpr int kGaussMutexDevices = 64;
+
 void gaussian_smooth_panels(double *data, double *tmp, int panels, int n0, int n1, double sigma, cudaStream_t stream) {
   if (!(sigma > 0.0)) return;
   int radius = 0;
   const std::vector<double> w = gaussian_weights(sigma, &radius);
   if (radius > kMaxRadius) throw invalid_argument("Gaussian smoothing: sigma too large (radius > 256 samples).");
   if (radius == 0) return;  // a single weight of 1
+  // c_gauss is ONE constant array per device: two models on the same GPU smoothing at once (different streams or host
+  // threads, different sigma) would read each other's weights.  The call is synchronous anyway, so it holds the
+  // device's lock from the upload to the end of the second pass.
+  static std::mutex gauss_mutex[kGaussMutexDevices];
+  int device = 0;
+  PSV_CUDA(cudaGetDevice(&device));
+  std::lock_guard<std::mutex> lock(gauss_mutex[device >= 0 && device < kGaussMutexDevices ? device : 0]);
   PSV_CUDA(cudaMemcpyToSymbolAsync(c_gauss, w.data(), w.size() * sizeof(double), 0, cudaMemcpyHostToDevice, stream));
   const size_t total = (size_t)panels * n0 * n1;
   gauss_axis_kernel<<<blocks(total, 256), 256, 0, stream>>>(data, tmp, panels, n0, n1, 0, radius);
@@ -225,7 +235,13 @@ LbfgsResult lbfgs_minimize(double *x, size_t n, const std::function<double(const
       double t = std::isfinite(fn) ? -dg * step * step / (2.0 * (fn - f - dg * step)) : 0.1 * step;
       step = std::min(0.5 * step, std::max(0.1 * step, t));
     }
-    if (!ok) break;  // no decrease along a descent direction: the gradient is as good as it gets
+    if (!ok) {  // no decrease along a descent direction: the gradient is as good as it gets
+      // the last evaluation was a REJECTED trial point: evaluate x once more so that everything the evaluation leaves
+      // behind in the caller's object (synthetics, sensitivity kernels, misfit) belongs to the point that is returned
+      evaluate(x, gn);
+      ++res.evaluations;
+      break;
+    }
     // s = xn - x, y = gn - g
     double *s = S + (size_t)head * n, *y = Y + (size_t)head * n;
     PSV_CUDA(cudaMemcpyAsync(s, xn, n * sizeof(double), cudaMemcpyDeviceToDevice, stream));
