@@ -203,3 +203,13 @@ def test_gaussian_weights_are_scipys(lib, sigma):
     assert abs(got.sum() - 1.0) <= 4e-16
     assert lib.psv_gaussian_weights(-1.0, buf, 4096, C.byref(radius)) != 0
     assert lib.psv_gaussian_weights(sigma, buf, 1, C.byref(radius)) != 0  # capacity too small
+
+
+def test_reference_import_names_resolve_to_this_library():
+    """`import psvWave` / top-level `__psvWave_cpp` (psvWave/__init__.py:6 of the reference) are this library."""
+    import __psvWave_cpp
+    import psvWave
+    import psvwave_b200
+    assert psvWave.fdModel is psvwave_b200.fdModel is __psvWave_cpp.fdModel
+    assert psvWave.get_dictionary()["domain"]["nt"] == psvwave_b200.get_dictionary()["domain"]["nt"]
+    assert os.path.exists(os.path.join(ROOT, "tests", "test_configurations", "default_testing_configuration.ini"))
