@@ -441,6 +441,51 @@ def extra_default_config() -> dict:
             "timing": "CUDA events around each time loop; host clock around the whole gradient, best of 3"}
 
 
+def extra_monte_carlo(n_models: int = 64) -> dict:
+    """BASELINE.json configs[3]: an ensemble of media on the reference's default configuration, all
+    forward-simulated together by psv_forward_batch (the reference's route: n copies of the object run one after the
+    other, src/fdModel.cpp:64-97).  Device time of the whole ensemble from CUDA events on the leader's stream."""
+    import psvwave_b200
+    ini = os.path.join(ROOT, "configs", "default_testing_configuration.ini")
+    rng = np.random.default_rng(2024)
+
+    def smooth(a, n=6):
+        for _ in range(n):
+            a = (a + np.roll(a, 1, 0) + np.roll(a, -1, 0) + np.roll(a, 1, 1) + np.roll(a, -1, 1)) / 5.0
+        return a
+
+    models = []
+    for _ in range(n_models):
+        x = psvwave_b200.fdModel(ini)
+        f = [1 + 0.05 * smooth(rng.standard_normal((x.nx, x.nz))) / 0.2 for _ in range(3)]
+        x.set_parameter_fields(2000.0 * f[0], 800.0 * f[1], 1500.0 * f[2])
+        models.append(x)
+    lead = models[0]
+    psvwave_b200.forward_batch(models, 0, False)  # warm-up
+    best = None
+    for _ in range(2):
+        psvwave_b200.forward_batch(models, 0, False)
+        dev = lead._get_stat("elapsed_ms") * 1e-3
+        best = dev if best is None else min(best, dev)
+    # parity: two members of the ensemble against the same media simulated on their own (same kernels: bit for bit)
+    same = True
+    for k in (1, n_models - 1):
+        ux, uz = (np.array(a) for a in models[k].get_synthetic_data())
+        solo = psvwave_b200.fdModel(ini)
+        solo._set_option("resident", 0)
+        solo.set_parameter_fields(*models[k].get_parameter_fields())
+        solo.forward_simulate(0, False)
+        sx, sz = solo.get_synthetic_data()
+        same = same and bool(np.array_equal(ux, sx) and np.array_equal(uz, sz))
+        del solo
+    pts = float(lead.nx) * lead.nz * lead.nt
+    return {"workload": "C4-monte-carlo-forward: models of default_testing_configuration.ini in one psv_forward_batch",
+            "models": n_models, "grid": [lead.nx, lead.nz], "nt": lead.nt, "seconds": best,
+            "models_per_s": n_models / best, "value": n_models * pts / best, "unit": "updates/s",
+            "parity": {"against": "members 1 and n-1 simulated on their own (per-step kernels)", "bit_identical": same},
+            "timing": "CUDA events around the ensemble's time loop, best of 2"}
+
+
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
@@ -622,7 +667,8 @@ def run_ours(args) -> None:
         barrier()
         if rank == 0:
             for name, fn in (("slab_split", extra_slab_split), ("one_object_all_gpus", extra_one_object),
-                             ("default_config", lambda n: extra_default_config())):
+                             ("default_config", lambda n: extra_default_config()),
+                             ("monte_carlo", lambda n: extra_monte_carlo())):
                 try:
                     extra[name] = fn(world)
                 except Exception as e:  # an extra never takes the headline down
