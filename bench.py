@@ -712,12 +712,17 @@ def run_ours(args) -> None:
         achieved = nbytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         traffic, traffic_source = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath) and not fp32:  # an ncu capture of the default FP64 step kernel, not of this run
+        traffic_stale = None
+        if os.path.exists(tpath):  # an ncu capture of the step kernel of ONE library build, not of this run
+            import hashlib
             tj = json.load(open(tpath))
-            traffic, traffic_source = tj.get(kern), "profiles/traffic.json (" + str(tj.get("_source", "ncu --set full")) + ")"
+            traffic = tj.get(kern + (" (fp32=1)" if fp32 else ""))
+            traffic_source = "profiles/traffic.json (" + str(tj.get("_source", "ncu --set full")) + ")"
+            sha = hashlib.sha256(open(psvwave_b200.LIBRARY_PATH, "rb").read()).hexdigest()[:16]
+            traffic_stale = bool(tj.get("_library_sha16") != sha)  # true: the capture is of another build of the library
         real = traffic if traffic else moved
         roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_source,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_source, "traffic_stale": traffic_stale,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": nbytes, "ms_per_launch": ms,
                     "note": "achieved/frac (= algorithmic_*) credit the single-pass ALGORITHMIC 128 B per update (SURVEY "
                             "8d) and can exceed 1 because the kernel moves fewer bytes (la, b_vz, taper are not "
