@@ -2,8 +2,9 @@
 compiled UNMODIFIED reference core (oracle/_ref, /root/reference/src/fdModel.cpp:526-969 forward + adjoint loops) on
 
   * the bench workload's grid (3100 x 1320, `bench.workload_config`: `marmousi_like` medium, 300 receivers,
-    snapshot every 20 steps) -- the launch geometry bench.py times: 8 consumer warps per CTA, multi-row strips on
-    every SM, 16-segment correlation slots;
+    snapshot every 20 steps) -- with the launch geometry bench.py times (chosen by the tuner at the first time
+    loop: 3, 4 or 8 consumer warps per CTA, multi-row strips on every SM; the geometry that ran is recorded) and
+    with each compiled CTA width pinned;
   * the C5 grid (8100 x 4100, BASELINE.json configs[4]), whole and cut into 2 and 4 in-process x-slabs with halo
     exchange (psvwave_b200.SlabDomain).
 
@@ -120,14 +121,35 @@ def bench_grid(tmp_path_factory):
 
 
 @pytest.mark.parametrize("exact", [0, 1], ids=["default-arithmetic", "exact"])
-def test_bench_grid_vs_compiled_reference(bench_grid, exact):
+def test_bench_grid_vs_compiled_reference(bench_grid, exact, record_property):
+    """The default configuration: the launch geometry is whatever the tuner measures on this box at the first time
+    loop (option "tune" = -1 on a grid this size); the geometry that actually ran is recorded with the result."""
     import psvwave_b200
     m = psvwave_b200.fdModel(bench_grid["ini"])
-    assert (m.nx, m.nz) == (3100, 1320) and m._get_option("variant") == 3 and m._get_option("pipe_warps") == 8
+    assert (m.nx, m.nz) == (3100, 1320) and m._get_option("variant") == 3 and m._get_option("tune") == -1
     m._set_option("exact", exact)
     m.set_parameter_fields(*bench_grid["medium"])
     run_workflow(m)
+    warps, strip = int(m._get_stat("tuned_warps")), int(m._get_stat("tuned_strip"))
+    record_property("tuned_warps", warps)
+    record_property("tuned_strip", strip)
+    print(f"geometry that ran: {warps} consumer warps per CTA, strips of {strip} rows")
+    assert warps in (3, 4, 8) and strip >= 1  # one of the compiled widths, chosen by measurement
     compare_whole(m, bench_grid["ref"], bench_grid["snaps"], bool(exact))
+
+
+@pytest.mark.parametrize("warps", [3, 4, 8])
+def test_bench_grid_every_compiled_width_vs_compiled_reference(bench_grid, warps):
+    """Each compiled CTA width pinned (tuner off), so that the geometry the tuner did NOT pick on this box is compared
+    with the reference on the bench grid as well."""
+    import psvwave_b200
+    m = psvwave_b200.fdModel(bench_grid["ini"])
+    m._set_option("tune", 0)
+    m._set_option("pipe_warps", warps)
+    m.set_parameter_fields(*bench_grid["medium"])
+    run_workflow(m)
+    assert m._get_option("pipe_warps") == warps
+    compare_whole(m, bench_grid["ref"], bench_grid["snaps"], False)
 
 
 # ---- the C5 grid, whole and split ----------------------------------------------------------------------------------
